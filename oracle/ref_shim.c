@@ -1,0 +1,148 @@
+/* oracle/ref_shim.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * Flat, ctypes-friendly entry points over the UNMODIFIED reference library (vendored c-blosc2 compiled by
+ * oracle/Makefile into oracle/_ref/libblosc2_ref.so).  This file is ours; it only #includes the reference's
+ * public header where it lies under /root/reference and calls the same functions the reference wrapper calls
+ * (compressed_image/include/compressed/blosc2/wrapper.h:134-277, 338-413), with the same cparams the
+ * wrapper builds (wrapper.h:338-359: BLOSC2_CPARAMS_DEFAULTS + blocksize, typesize, BLOSC_AUTO_SPLIT,
+ * clevel, nthreads, compcode), plus an explicit filter knob (filters[5]) for the bit-shuffle config.
+ *
+ * The *_batch entry points are the "R2" CPU baseline of SURVEY.md section 8(d): one nthreads=1 context per
+ * host thread, chunks dealt round-robin over all threads.
+ */
+#include <blosc2.h>
+#include <pthread.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+static blosc2_context* make_cctx(int codec, int clevel, int typesize, int filter, int blocksize, int nthreads) {
+  blosc2_cparams cp = BLOSC2_CPARAMS_DEFAULTS;
+  cp.blocksize = blocksize;
+  cp.typesize = typesize;
+  cp.splitmode = BLOSC_AUTO_SPLIT;
+  cp.clevel = (uint8_t)clevel;
+  cp.nthreads = (int16_t)(nthreads < 1 ? 1 : nthreads);
+  cp.compcode = (uint8_t)codec;
+  cp.filters[BLOSC2_MAX_FILTERS - 1] = (uint8_t)filter;
+  return blosc2_create_cctx(cp);
+}
+
+static blosc2_context* make_dctx(int nthreads) {
+  blosc2_dparams dp = BLOSC2_DPARAMS_DEFAULTS;
+  dp.nthreads = (int16_t)(nthreads < 1 ? 1 : nthreads);
+  return blosc2_create_dctx(dp);
+}
+
+int ref_compress(int codec, int clevel, int typesize, int filter, int blocksize, int nthreads,
+                 const void* src, int32_t nbytes, void* dst, int32_t cap) {
+  blosc2_context* c = make_cctx(codec, clevel, typesize, filter, blocksize, nthreads);
+  if (!c) return -1000;
+  int r = blosc2_compress_ctx(c, src, nbytes, dst, cap);
+  blosc2_free_ctx(c);
+  return r;
+}
+
+int ref_decompress(const void* src, int32_t srcsize, void* dst, int32_t cap, int nthreads) {
+  blosc2_context* c = make_dctx(nthreads);
+  if (!c) return -1000;
+  int r = blosc2_decompress_ctx(c, src, srcsize, dst, cap);
+  blosc2_free_ctx(c);
+  return r;
+}
+
+int ref_cbuffer_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes, int32_t* blocksize) {
+  return blosc2_cbuffer_sizes(chunk, nbytes, cbytes, blocksize);
+}
+
+typedef struct {
+  int tid, nworkers, n, compress;
+  int codec, clevel, typesize, filter, blocksize;
+  const void* const* srcs;
+  const int32_t* sizes;
+  void* const* dsts;
+  const int32_t* caps;
+  int32_t* out;
+} job_t;
+
+static void* worker(void* p) {
+  job_t* j = (job_t*)p;
+  blosc2_context* c = j->compress ? make_cctx(j->codec, j->clevel, j->typesize, j->filter, j->blocksize, 1)
+                                  : make_dctx(1);
+  for (int i = j->tid; i < j->n; i += j->nworkers) {
+    if (j->compress)
+      j->out[i] = blosc2_compress_ctx(c, j->srcs[i], j->sizes[i], j->dsts[i], j->caps[i]);
+    else
+      j->out[i] = blosc2_decompress_ctx(c, j->srcs[i], j->sizes[i], j->dsts[i], j->caps[i]);
+  }
+  blosc2_free_ctx(c);
+  return NULL;
+}
+
+static int run_batch(job_t proto, int nworkers) {
+  if (nworkers < 1) nworkers = 1;
+  if (nworkers > proto.n) nworkers = proto.n > 0 ? proto.n : 1;
+  pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * nworkers);
+  job_t* jobs = (job_t*)malloc(sizeof(job_t) * nworkers);
+  for (int t = 0; t < nworkers; t++) {
+    jobs[t] = proto;
+    jobs[t].tid = t;
+    jobs[t].nworkers = nworkers;
+    pthread_create(&th[t], NULL, worker, &jobs[t]);
+  }
+  for (int t = 0; t < nworkers; t++) pthread_join(th[t], NULL);
+  free(th);
+  free(jobs);
+  return 0;
+}
+
+int ref_compress_batch(int codec, int clevel, int typesize, int filter, int blocksize, int n,
+                       const void* const* srcs, const int32_t* nbytes, void* const* dsts, const int32_t* caps,
+                       int32_t* out_cbytes, int nworkers) {
+  job_t j = {0, 0, n, 1, codec, clevel, typesize, filter, blocksize, srcs, nbytes, dsts, caps, out_cbytes};
+  return run_batch(j, nworkers);
+}
+
+int ref_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes, void* const* dsts,
+                         const int32_t* caps, int32_t* out_nbytes, int nworkers) {
+  job_t j = {0, 0, n, 0, 0, 0, 0, 0, 0, srcs, srcsizes, dsts, caps, out_nbytes};
+  return run_batch(j, nworkers);
+}
+
+/* Raw stream codecs + filters of the reference, for pinning the restatement one layer at a time. */
+extern int LZ4_compress_fast(const char*, char*, int, int, int);
+extern int LZ4_decompress_safe(const char*, char*, int, int);
+extern int LZ4_compress_HC(const char*, char*, int, int, int);
+extern int blosclz_compress(int, const void*, int, void*, int, blosc2_context*);
+extern int blosclz_decompress(const void*, int, void*, int);
+extern size_t ZSTD_compress(void*, size_t, const void*, size_t, int);
+extern size_t ZSTD_decompress(void*, size_t, const void*, size_t);
+extern unsigned ZSTD_isError(size_t);
+extern void shuffle(int32_t, int32_t, const uint8_t*, uint8_t*);
+extern void unshuffle(int32_t, int32_t, const uint8_t*, uint8_t*);
+extern int32_t bitshuffle(int32_t, int32_t, const uint8_t*, uint8_t*);
+extern int32_t bitunshuffle(int32_t, int32_t, const uint8_t*, uint8_t*, uint8_t);
+
+int ref_lz4_compress(const void* s, int n, void* d, int cap) { return LZ4_compress_fast(s, d, n, cap, 1); }
+int ref_lz4hc_compress(const void* s, int n, void* d, int cap, int lvl) { return LZ4_compress_HC(s, d, n, cap, lvl); }
+int ref_lz4_decompress(const void* s, int n, void* d, int cap) { return LZ4_decompress_safe(s, d, n, cap); }
+int ref_blosclz_compress(int clevel, int typesize, int filter, const void* s, int n, void* d, int cap) {
+  /* blosclz reads ctx->src (NULL check only), ctx->typesize, ctx->filter_flags... give it a real context. */
+  blosc2_context* c = make_cctx(BLOSC_BLOSCLZ, clevel, typesize, filter, 0, 1);
+  int r = blosclz_compress(clevel, s, n, d, cap, c);
+  blosc2_free_ctx(c);
+  return r;
+}
+int ref_blosclz_decompress(const void* s, int n, void* d, int cap) { return blosclz_decompress(s, n, d, cap); }
+long ref_zstd_compress(const void* s, long n, void* d, long cap, int lvl) {
+  size_t r = ZSTD_compress(d, cap, s, n, lvl);
+  return ZSTD_isError(r) ? -1 : (long)r;
+}
+long ref_zstd_decompress(const void* s, long n, void* d, long cap) {
+  size_t r = ZSTD_decompress(d, cap, s, n);
+  return ZSTD_isError(r) ? -1 : (long)r;
+}
+int ref_shuffle(int ts, int n, const void* s, void* d) { shuffle(ts, n, s, d); return n; }
+int ref_unshuffle(int ts, int n, const void* s, void* d) { unshuffle(ts, n, s, d); return n; }
+int ref_bitshuffle(int ts, int n, const void* s, void* d) { return bitshuffle(ts, n, s, d); }
+int ref_bitunshuffle(int ts, int n, const void* s, void* d, int ver) { return bitunshuffle(ts, n, s, d, (uint8_t)ver); }
