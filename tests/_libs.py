@@ -86,3 +86,51 @@ def ref():
 def ptr(a):
     """Address of a numpy array's buffer (0-size arrays get a valid dummy address)."""
     return a.ctypes.data
+
+
+# ---- numpy-level helpers over the two checkers -------------------------------------------------------------
+import numpy as np  # noqa: E402
+
+
+def ref_sizes(chunk):
+    R = ref()
+    nb, cb, bs = i32(), i32(), i32()
+    R.ref_cbuffer_sizes(ptr(chunk), C.byref(nb), C.byref(cb), C.byref(bs))
+    return nb.value, cb.value, bs.value
+
+
+def ref_compress(codec, clevel, typesize, filt, blocksize, src, nthreads=1):
+    R = ref()
+    src = np.ascontiguousarray(src).view(np.uint8).reshape(-1)
+    dst = np.zeros(src.size + 32, dtype=np.uint8)
+    r = R.ref_compress(codec, clevel, typesize, filt, blocksize, nthreads, ptr(src), int(src.size), ptr(dst),
+                       int(dst.size))
+    assert r > 0, r
+    return dst[:r].copy()
+
+
+def ref_decompress(chunk, cap=None):
+    """-> (rc, bytes).  rc < 0 is the reference's error code."""
+    R = ref()
+    chunk = np.ascontiguousarray(chunk)
+    nb = int.from_bytes(chunk[4:8].tobytes(), "little", signed=True) if cap is None else cap
+    out = np.zeros(max(nb, 1), dtype=np.uint8)
+    r = R.ref_decompress(ptr(chunk), int(chunk.size), ptr(out), int(nb), 1)
+    return r, out[:max(r, 0)]
+
+
+def oracle_compress(codec, clevel, typesize, filt, blocksize, src, cap=None):
+    O = oracle()
+    src = np.ascontiguousarray(src).view(np.uint8).reshape(-1)
+    dst = np.zeros((src.size + 32) if cap is None else cap, dtype=np.uint8)
+    r = O.b2o_compress(codec, clevel, typesize, filt, blocksize, ptr(src), int(src.size), ptr(dst), int(dst.size))
+    return r, dst[:max(r, 0)].copy()
+
+
+def oracle_decompress(chunk, cap=None):
+    O = oracle()
+    chunk = np.ascontiguousarray(chunk)
+    nb = int.from_bytes(chunk[4:8].tobytes(), "little", signed=True) if cap is None else cap
+    out = np.zeros(max(nb, 1), dtype=np.uint8)
+    r = O.b2o_decompress(ptr(chunk), int(chunk.size), ptr(out), int(nb))
+    return r, out[:max(r, 0)]
