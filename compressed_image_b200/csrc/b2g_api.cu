@@ -1,0 +1,532 @@
+// b2g_api.cu -- host side of the C ABI declared in include/b2g.h: contexts, batch planning, stream-ordered
+// staging and kernel launches.  No CPU codec lives here: every byte of (de)compression happens in the sm_100a
+// kernels of b2g_kernels.cuh; without a usable CUDA device every data call fails with B2G_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b2g.h"
+#include "b2g_kernels.cuh"
+#include "b2g_plan.h"
+
+using namespace b2g;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+bool cuda_fail(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return false;
+  g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
+  return true;
+}
+#define CU(call)                                  \
+  do {                                            \
+    if (cuda_fail((call), #call)) return B2G_ERR_NO_DEVICE; \
+  } while (0)
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    want += want / 4;
+    if (cuda_fail(cudaMalloc(&p, want), "cudaMalloc")) return B2G_ERR_NO_DEVICE;
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct HostBuf {  // pinned
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    want += want / 4;
+    if (cuda_fail(cudaHostAlloc(&p, want, cudaHostAllocDefault), "cudaHostAlloc")) return B2G_ERR_NO_DEVICE;
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
+constexpr size_t kDecodeSharedBytes = 256;  // DecodeShared, padded
+constexpr size_t kCompressSharedBytes = 256;
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct b2g_ctx {
+  b2g_params p{};
+  int dev = 0, sms = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  float last_ms[2] = {0, 0};
+  int64_t launches = 0;
+  // geometry
+  int blocksize = 32768;   // context blocksize (compress) / largest block the device decode path is sized for
+  int win_bytes = 32768;   // shared-memory window
+  size_t dec_smem = 0, decz_smem = 0, comp_smem = 0;
+  int dec_grid = 0, decz_grid = 0, comp_grid = 0;
+  bool geometry_ready = false;
+  // device + pinned work buffers
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_desc, d_slab, d_in, d_out;
+  HostBuf h_chunks, h_res, h_cinfo, h_base;
+  // in-flight batch (device-resident API)
+  b2g_chunk* pend = nullptr;
+  int pend_n = 0;
+  cudaStream_t pend_stream = nullptr;
+};
+
+namespace {
+
+int set_geometry(b2g_ctx* c, int blocksize) {
+  // (re)derive shared-memory sizes, grids and the slab for a given maximum blocksize
+  if (c->geometry_ready && blocksize <= c->blocksize) return 0;
+  c->blocksize = std::max(blocksize, 1);
+  const int win = (int)align_up((size_t)std::min(c->blocksize, kMaxSmemWindow), 16);
+  c->win_bytes = std::max(win, 1024);
+  c->dec_smem = (size_t)c->win_bytes + kDecodeSharedBytes;
+  c->decz_smem = (size_t)c->win_bytes + kDecodeSharedBytes + sizeof(ZWork) * kCtaWarps;
+  c->comp_smem = (size_t)c->win_bytes + (size_t)plan_htab_bytes(c->win_bytes) + kCompressSharedBytes;
+  CU(cudaFuncSetAttribute(k_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->dec_smem));
+  CU(cudaFuncSetAttribute(k_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->decz_smem));
+  if (c->comp_smem <= 227 * 1024)
+    CU(cudaFuncSetAttribute(k_compress, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->comp_smem));
+  if (c->win_bytes <= 227 * 1024)
+    CU(cudaFuncSetAttribute(k_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, c->win_bytes));
+  int occ = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, kCtaThreads, c->dec_smem));
+  c->dec_grid = c->sms * std::max(occ, 1);
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, kCtaThreads, c->decz_smem));
+  c->decz_grid = c->sms * std::max(occ, 1);
+  occ = 0;
+  if (c->comp_smem <= 227 * 1024)
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, kCtaThreads, c->comp_smem));
+  c->comp_grid = c->sms * std::max(occ, 1);
+  // slab: compressed streams of one block per compress CTA; whole blocks for oversized decode blocks
+  const size_t stride = align_up((size_t)c->blocksize + 16 * kMaxStreams + 256, 256);
+  const int grid = std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid));
+  if (int rc = c->d_slab.ensure(stride * (size_t)grid)) return rc;
+  c->geometry_ready = true;
+  return 0;
+}
+
+size_t slab_stride(const b2g_ctx* c) { return align_up((size_t)c->blocksize + 16 * kMaxStreams + 256, 256); }
+
+int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd) {
+  if (int rc = c->d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  if (int rc = c->d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
+  if (int rc = c->d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (int rc = c->d_base.ensure(sizeof(int32_t) * 2 * ((size_t)n + 1))) return rc;
+  if (int rc = c->d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
+  if (int rc = c->h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  CU(cudaMemcpyAsync(c->d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(c->ev[0], s));
+  PlanArgs pa;
+  pa.chunks = (const DChunk*)c->d_chunks.p;
+  pa.info = (DInfo*)c->d_info.p;
+  pa.res = (DResult*)c->d_res.p;
+  pa.base = (int32_t*)c->d_base.p;
+  pa.ctl = (BatchCtl*)c->d_ctl.p;
+  pa.n = n;
+  pa.max_block = c->blocksize;
+  pa.zstd_ok = want_zstd ? 1 : 0;
+  k_plan_decode<<<1, 1024, 2 * 1024 * sizeof(int32_t), s>>>(pa);
+  c->launches++;
+  CU(cudaEventRecord(c->ev[1], s));
+  DecodeArgs da;
+  da.chunks = pa.chunks;
+  da.info = pa.info;
+  da.res = pa.res;
+  da.base = pa.base;
+  da.ctl = pa.ctl;
+  da.n = n;
+  da.win_bytes = c->win_bytes;
+  da.slab = (uint8_t*)c->d_slab.p;
+  da.slab_stride = (int64_t)slab_stride(c);
+  k_decode<false><<<c->dec_grid, kCtaThreads, c->dec_smem, s>>>(da);
+  c->launches++;
+  if (want_zstd) {
+    da.base = pa.base + (n + 1);
+    da.ctl = pa.ctl + 1;
+    k_decode<true><<<c->decz_grid, kCtaThreads, c->decz_smem, s>>>(da);
+    c->launches++;
+  }
+  CU(cudaEventRecord(c->ev[2], s));
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_res.p, c->d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  return 0;
+}
+
+int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
+  const b2g_params& p = c->p;
+  if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
+  if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
+  if (p.clevel > 9) return B2G_ERR_CODEC_PARAM;
+  if (c->comp_smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
+  if (int rc = c->h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+  if (int rc = c->h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
+  CInfo* ci = (CInfo*)c->h_cinfo.p;
+  int32_t* base = (int32_t*)c->h_base.p;
+  int64_t items = 0;
+  CParams cp;
+  cp.codec = p.codec; cp.clevel = p.clevel; cp.typesize = p.typesize; cp.filter = p.filter;
+  for (int i = 0; i < n; i++) {
+    const int nit = plan_compress_chunk(ci[i], cp, c->p.blocksize, nbytes[i], h_desc[i].dst_cap, c->win_bytes);
+    ci[i].item_base = (int32_t)items;
+    base[i] = (int32_t)items;
+    items += nit;
+    if (items > INT32_MAX) return B2G_ERR_MAX_BUFSIZE;
+  }
+  base[n] = (int32_t)items;
+  if (int rc = c->d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  if (int rc = c->d_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+  if (int rc = c->d_state.ensure(sizeof(CState) * (size_t)n)) return rc;
+  if (int rc = c->d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (int rc = c->d_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
+  if (int rc = c->d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
+  if (int rc = c->d_desc.ensure(sizeof(unsigned long long) * (size_t)items)) return rc;
+  if (int rc = c->h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  CU(cudaMemcpyAsync(c->d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(c->d_cinfo.p, ci, sizeof(CInfo) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(c->d_base.p, base, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(c->ev[0], s));
+  CU(cudaMemsetAsync(c->d_state.p, 0, sizeof(CState) * (size_t)n, s));
+  CU(cudaMemsetAsync(c->d_desc.p, 0, sizeof(unsigned long long) * (size_t)items, s));
+  CU(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(BatchCtl) * 2, s));
+  CU(cudaMemcpyAsync(c->d_ctl.p, &base[n], sizeof(int32_t), cudaMemcpyHostToDevice, s));  // ctl[0].total_items
+  CU(cudaEventRecord(c->ev[1], s));
+  CompressArgs ca;
+  ca.chunks = (const DChunk*)c->d_chunks.p;
+  ca.info = (const CInfo*)c->d_cinfo.p;
+  ca.state = (CState*)c->d_state.p;
+  ca.base = (const int32_t*)c->d_base.p;
+  ca.ctl = (BatchCtl*)c->d_ctl.p;
+  ca.desc = (unsigned long long*)c->d_desc.p;
+  ca.slab = (uint8_t*)c->d_slab.p;
+  ca.slab_stride = (int64_t)slab_stride(c);
+  ca.n = n;
+  ca.win_bytes = c->win_bytes;
+  ca.htab_bytes = plan_htab_bytes(c->win_bytes);
+  ca.p = cp;
+  const int cgrid = (int)std::min<int64_t>(c->comp_grid, items);
+  k_compress<<<cgrid, kCtaThreads, c->comp_smem, s>>>(ca);
+  c->launches++;
+  FinalizeArgs fa;
+  fa.chunks = ca.chunks;
+  fa.info = ca.info;
+  fa.state = ca.state;
+  fa.res = (DResult*)c->d_res.p;
+  fa.base = ca.base;
+  fa.n = n;
+  fa.total_items = (int32_t)items;
+  fa.p = ca.p;
+  const int fgrid = (int)std::min<int64_t>((int64_t)c->sms * 16, items);
+  k_finalize<<<fgrid, kCtaThreads, 0, s>>>(fa);
+  c->launches++;
+  CU(cudaEventRecord(c->ev[2], s));
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_res.p, c->d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  return 0;
+}
+
+int finish(b2g_ctx* c, b2g_chunk* chunks, int n, cudaStream_t s) {
+  CU(cudaStreamSynchronize(s));
+  const DResult* r = (const DResult*)c->h_res.p;
+  for (int i = 0; i < n; i++) {
+    chunks[i].status = r[i].status;
+    chunks[i].out_bytes = r[i].status < 0 ? 0 : r[i].out_bytes;
+  }
+  float a = 0, b = 0;
+  if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) c->last_ms[0] = a;
+  if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) c->last_ms[1] = b;
+  return 0;
+}
+
+int use_device(b2g_ctx* c) {
+  CU(cudaSetDevice(c->dev));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+b2g_ctx* b2g_create(const b2g_params* params) {
+  if (!params) { g_last_error = "b2g_create: params == NULL"; return nullptr; }
+  int ndev = 0;
+  if (cuda_fail(cudaGetDeviceCount(&ndev), "cudaGetDeviceCount") || ndev == 0) {
+    if (g_last_error.empty()) g_last_error = "no CUDA device";
+    return nullptr;
+  }
+  b2g_ctx* c = new b2g_ctx();
+  c->p = *params;
+  if (c->p.typesize == 0) c->p.typesize = 1;
+  if (c->p.blocksize <= 0) c->p.blocksize = 32768;
+  int dev = params->device;
+  if (dev < 0 && cuda_fail(cudaGetDevice(&dev), "cudaGetDevice")) { delete c; return nullptr; }
+  c->dev = dev;
+  bool ok = !cuda_fail(cudaSetDevice(dev), "cudaSetDevice") &&
+            !cuda_fail(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev), "sm count") &&
+            !cuda_fail(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+  for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&c->ev[i]), "cudaEventCreate");
+  if (ok) ok = set_geometry(c, c->p.blocksize) == 0;
+  if (!ok) { b2g_destroy(c); return nullptr; }
+  return c;
+}
+
+void b2g_destroy(b2g_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->dev);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  for (DevBuf* b : {&c->d_chunks, &c->d_info, &c->d_res, &c->d_base, &c->d_ctl, &c->d_cinfo, &c->d_state, &c->d_desc,
+                    &c->d_slab, &c->d_in, &c->d_out})
+    b->release();
+  for (HostBuf* b : {&c->h_chunks, &c->h_res, &c->h_cinfo, &c->h_base}) b->release();
+  for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int b2g_decompress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (c->pend) return B2G_ERR_FAILURE;
+  if (int rc = use_device(c)) return rc;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  c->pend = chunks; c->pend_n = n; c->pend_stream = s;
+  if (n == 0) return 0;
+  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n)) { c->pend = nullptr; return rc; }
+  DChunk* h = (DChunk*)c->h_chunks.p;
+  for (int i = 0; i < n; i++) {
+    h[i].src = (const uint8_t*)chunks[i].src;
+    h[i].dst = (uint8_t*)chunks[i].dst;
+    h[i].src_bytes = chunks[i].src_bytes;
+    h[i].dst_cap = chunks[i].dst_capacity;
+  }
+  int rc = enqueue_decode(c, h, n, s, c->p.codec == B2G_ZSTD);
+  if (rc) c->pend = nullptr;
+  return rc;
+}
+
+int b2g_compress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (c->pend) return B2G_ERR_FAILURE;
+  if (int rc = use_device(c)) return rc;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  c->pend = chunks; c->pend_n = n; c->pend_stream = s;
+  if (n == 0) return 0;
+  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n + sizeof(int32_t) * (size_t)n)) { c->pend = nullptr; return rc; }
+  DChunk* h = (DChunk*)c->h_chunks.p;
+  int32_t* nb = (int32_t*)(h + n);
+  for (int i = 0; i < n; i++) {
+    h[i].src = (const uint8_t*)chunks[i].src;
+    h[i].dst = (uint8_t*)chunks[i].dst;
+    h[i].src_bytes = chunks[i].src_bytes;
+    h[i].dst_cap = chunks[i].dst_capacity;
+    nb[i] = chunks[i].src_bytes;
+  }
+  int rc = enqueue_compress(c, h, nb, n, s);
+  if (rc) c->pend = nullptr;
+  return rc;
+}
+
+int b2g_wait(b2g_ctx* c) {
+  if (!c) return B2G_ERR_INVALID_PARAM;
+  if (!c->pend) return 0;
+  if (int rc = use_device(c)) return rc;
+  b2g_chunk* chunks = c->pend;
+  int n = c->pend_n;
+  c->pend = nullptr;
+  if (n == 0) return 0;
+  return finish(c, chunks, n, c->pend_stream);
+}
+
+int b2g_chunk_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes, int32_t* blocksize) {
+  // blosc2_cbuffer_sizes (blosc2.c:3696-3712) + the header checks of read_chunk_header (blosc2.c:672-711)
+  const uint8_t* s = (const uint8_t*)chunk;
+  int32_t nb, bs, cb;
+  memcpy(&nb, s + 4, 4); memcpy(&bs, s + 8, 4); memcpy(&cb, s + 12, 4);
+  int rc = 0;
+  if (s[0] > 5) rc = B2G_ERR_VERSION_SUPPORT;
+  else if (cb < kHdrMin) rc = B2G_ERR_INVALID_HEADER;
+  else if (bs <= 0 || (nb > 0 && bs > nb)) rc = B2G_ERR_INVALID_HEADER;
+  else if (bs > kMaxBlocksize) rc = B2G_ERR_INVALID_HEADER;
+  else if (s[3] == 0) rc = B2G_ERR_INVALID_HEADER;
+  if (rc < 0) nb = cb = bs = 0;
+  if (nbytes) *nbytes = nb;
+  if (cbytes) *cbytes = cb;
+  if (blocksize) *blocksize = bs;
+  return rc;
+}
+
+int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (c->pend) return B2G_ERR_FAILURE;
+  if (n == 0) return 0;
+  if (int rc = use_device(c)) return rc;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  DChunk* h = (DChunk*)c->h_chunks.p;
+  std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n);
+  size_t in_total = 0, out_total = 0;
+  int maxblock = 0;
+  bool any_zstd = false;
+  for (int i = 0; i < n; i++) {
+    const uint8_t* src = (const uint8_t*)chunks[i].src;
+    int32_t avail = chunks[i].src_bytes;
+    int32_t nb = 0, cb = 0, bs = 0;
+    size_t take = 0, give = 0;
+    if (src && avail >= kHdrMin) {
+      memcpy(&nb, src + 4, 4); memcpy(&bs, src + 8, 4); memcpy(&cb, src + 12, 4);
+      take = (size_t)std::max(kHdrMin, std::min(avail, cb < kHdrMin ? kHdrExt : cb));  // INT32_MAX: trust the header
+      if (avail != INT32_MAX) take = std::min(take, (size_t)avail);
+      if (nb > 0 && nb <= chunks[i].dst_capacity) give = (size_t)nb;
+      if (bs > 0 && bs <= kMaxBlocksize) maxblock = std::max(maxblock, bs);
+      if ((src[2] >> 5) == kFmtZstd) any_zstd = true;
+    } else if (src && avail > 0) {
+      take = (size_t)avail;
+    }
+    in_off[i] = in_total; in_len[i] = take; in_total += align_up(take + 8, 256);
+    out_off[i] = out_total; out_len[i] = give; out_total += align_up(give + 8, 256);
+  }
+  if (int rc = set_geometry(c, std::max(maxblock, c->blocksize))) return rc;
+  if (int rc = c->d_in.ensure(in_total + 256)) return rc;
+  if (int rc = c->d_out.ensure(out_total + 256)) return rc;
+  for (int i = 0; i < n; i++) {
+    h[i].src = (const uint8_t*)c->d_in.p + in_off[i];
+    h[i].dst = (uint8_t*)c->d_out.p + out_off[i];
+    h[i].src_bytes = chunks[i].src_bytes == INT32_MAX ? (int32_t)in_len[i] : std::min<int32_t>(chunks[i].src_bytes, (int32_t)in_len[i]);
+    h[i].dst_cap = chunks[i].dst_capacity;
+    if (in_len[i])
+      CU(cudaMemcpyAsync((void*)h[i].src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
+  }
+  if (int rc = enqueue_decode(c, h, n, s, any_zstd)) return rc;
+  for (int i = 0; i < n; i++)
+    if (out_len[i]) CU(cudaMemcpyAsync(chunks[i].dst, h[i].dst, out_len[i], cudaMemcpyDeviceToHost, s));
+  return finish(c, chunks, n, s);
+}
+
+int b2g_compress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (c->pend) return B2G_ERR_FAILURE;
+  if (n == 0) return 0;
+  if (int rc = use_device(c)) return rc;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n + sizeof(int32_t) * (size_t)n)) return rc;
+  DChunk* h = (DChunk*)c->h_chunks.p;
+  int32_t* nb = (int32_t*)(h + n);
+  std::vector<size_t> in_off(n), out_off(n);
+  size_t in_total = 0, out_total = 0;
+  for (int i = 0; i < n; i++) {
+    const int32_t sz = std::max(chunks[i].src_bytes, 0);
+    const int32_t cap = std::max(std::min(chunks[i].dst_capacity, sz + B2G_MAX_OVERHEAD), 0);
+    in_off[i] = in_total; in_total += align_up((size_t)sz + 8, 256);
+    out_off[i] = out_total; out_total += align_up((size_t)cap + 8, 256);
+  }
+  if (int rc = c->d_in.ensure(in_total + 256)) return rc;
+  if (int rc = c->d_out.ensure(out_total + 256)) return rc;
+  for (int i = 0; i < n; i++) {
+    h[i].src = (const uint8_t*)c->d_in.p + in_off[i];
+    h[i].dst = (uint8_t*)c->d_out.p + out_off[i];
+    h[i].src_bytes = chunks[i].src_bytes;
+    h[i].dst_cap = std::min(chunks[i].dst_capacity, std::max(chunks[i].src_bytes, 0) + B2G_MAX_OVERHEAD);
+    nb[i] = chunks[i].src_bytes;
+    if (chunks[i].src_bytes > 0)
+      CU(cudaMemcpyAsync((void*)h[i].src, chunks[i].src, (size_t)chunks[i].src_bytes, cudaMemcpyHostToDevice, s));
+  }
+  if (int rc = enqueue_compress(c, h, nb, n, s)) return rc;
+  if (int rc = finish(c, chunks, n, s)) return rc;  // sizes are needed before the chunks can be copied back
+  for (int i = 0; i < n; i++)
+    if (chunks[i].out_bytes > 0)
+      CU(cudaMemcpyAsync(chunks[i].dst, h[i].dst, (size_t)chunks[i].out_bytes, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int b2g_filter_device(b2g_ctx* c, int filter, int forward, int typesize, int format_version, const void* src,
+                      void* dst, int64_t n, int32_t blocksize, void* cuda_stream) {
+  if (!c || n < 0 || blocksize <= 0 || typesize <= 0 || typesize > 255) return B2G_ERR_INVALID_PARAM;
+  if (filter < 0 || filter > 2) return B2G_ERR_FILTER_PIPELINE;
+  if (n == 0) return 0;
+  if (int rc = use_device(c)) return rc;
+  if (int rc = set_geometry(c, blocksize)) return rc;
+  if (blocksize > c->win_bytes) return B2G_ERR_BLOCKSIZE;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  FilterArgs fa;
+  fa.src = (const uint8_t*)src;
+  fa.dst = (uint8_t*)dst;
+  fa.n = n;
+  fa.blocksize = blocksize;
+  fa.typesize = typesize;
+  fa.filter = filter;
+  fa.forward = forward;
+  fa.version = format_version;
+  const int64_t nblocks = (n + blocksize - 1) / blocksize;
+  if (nblocks > INT32_MAX) return B2G_ERR_MAX_BUFSIZE;
+  fa.nblocks = (int32_t)nblocks;
+  const int grid = (int)std::min<int64_t>(nblocks, (int64_t)c->sms * 8);
+  k_filter<<<grid, kCtaThreads, (size_t)c->win_bytes, s>>>(fa);
+  c->launches++;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }
+
+int b2g_last_kernel_ms(const b2g_ctx* c, float out_ms[2]) {
+  if (!c || !out_ms) return B2G_ERR_INVALID_PARAM;
+  out_ms[0] = c->last_ms[0];
+  out_ms[1] = c->last_ms[1];
+  return 0;
+}
+
+const char* b2g_strerror(int code) {
+  switch (code) {
+    case B2G_OK: return "ok";
+    case B2G_ERR_FAILURE: return "generic failure";
+    case B2G_ERR_DATA: return "compressed data is corrupt (a stream did not decode to its block size)";
+    case B2G_ERR_READ_BUFFER: return "chunk is truncated";
+    case B2G_ERR_WRITE_BUFFER: return "destination buffer too small";
+    case B2G_ERR_CODEC_SUPPORT: return "codec not supported";
+    case B2G_ERR_CODEC_PARAM: return "invalid codec parameter";
+    case B2G_ERR_VERSION_SUPPORT: return "chunk format version not supported";
+    case B2G_ERR_INVALID_HEADER: return "invalid chunk header";
+    case B2G_ERR_INVALID_PARAM: return "invalid parameter";
+    case B2G_ERR_RUN_LENGTH: return "invalid run-length stream";
+    case B2G_ERR_FILTER_PIPELINE: return "filter pipeline not supported";
+    case B2G_ERR_MAX_BUFSIZE: return "buffer larger than 2 GiB - 32";
+    case B2G_ERR_NO_DEVICE: return "no usable CUDA device / CUDA runtime error";
+    case B2G_ERR_BLOCKSIZE: return "blocksize exceeds what this context was sized for";
+    case B2G_ERR_CTX_CODEC: return "zstd chunk on a context not created for zstd";
+    default: return "unknown error";
+  }
+}
+
+const char* b2g_last_error(void) { return g_last_error.c_str(); }
+
+int b2g_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+const char* b2g_version(void) { return "b2g 0.1.0 (sm_100a; blosc2 chunk format 5)"; }
+
+}  // extern "C"

@@ -3,8 +3,13 @@
 // Vocabulary follows blosc2: a CHUNK is split into BLOCKS (default 32 KiB); a block is stored as 1 or
 // `typesize` STREAMS (the byte planes of the shuffled block), each framed by an int32 csize
 // (reference: thirdparty/c-blosc2/blosc/blosc2.c:1080-1332 blosc_c, :1568-1937 blosc_d).
+//
+// The same sources compile two ways: with nvcc for sm_100a (the product), and with g++ under tests/sim/cusim.h
+// (B2G_SIM; a CPU fiber simulator used only by the test-suite to exercise this exact code without a GPU).
 #pragma once
+#ifndef B2G_SIM
 #include <cuda_runtime.h>
+#endif
 #include <stdint.h>
 
 namespace b2g {
@@ -13,13 +18,17 @@ constexpr int kHdrMin = 16, kHdrExt = 32;
 constexpr int kMaxStreams = 16;        // stune.h:24 MAX_STREAMS
 constexpr int kMinBuffer = 32;         // b2h:193 BLOSC_MIN_BUFFERSIZE
 constexpr int kMaxBlocksize = 536866816;
+constexpr int kCtaThreads = 128;       // every block-level kernel runs 4 warps per CTA
+constexpr int kCtaWarps = kCtaThreads / 32;
+constexpr unsigned kFull = 0xffffffffu;
 
 enum : uint8_t { kFlagShuffle = 1, kFlagMemcpyed = 2, kFlagBitshuffle = 4, kFlagDelta = 8, kFlagDontSplit = 0x10 };
 enum : uint8_t { kFmtBlosclz = 0, kFmtLz4 = 1, kFmtZlib = 3, kFmtZstd = 4 };
+enum : uint8_t { kCodecBlosclz = 0, kCodecLz4 = 1, kCodecLz4hc = 2, kCodecZstd = 5 };
 enum : uint8_t { kFilterNone = 0, kFilterShuffle = 1, kFilterBitshuffle = 2 };
-enum : int { kErrData = -3, kErrRead = -5, kErrWrite = -6, kErrCodec = -7, kErrCodecParam = -8, kErrVersion = -10,
-             kErrHeader = -11, kErrParam = -12, kErrRunLength = -17, kErrFilter = -18, kErrMaxBuf = -35,
-             kErrBlocksize = -101, kErrCtxCodec = -102 };
+enum : int { kErrFailure = -1, kErrData = -3, kErrRead = -5, kErrWrite = -6, kErrCodec = -7, kErrCodecParam = -8,
+             kErrVersion = -10, kErrHeader = -11, kErrParam = -12, kErrRunLength = -17, kErrFilter = -18,
+             kErrMaxBuf = -35, kErrBlocksize = -101, kErrCtxCodec = -102 };
 
 // One chunk of a batch as the kernels see it (device pointers).
 struct DChunk {
@@ -32,9 +41,16 @@ struct DChunk {
 // Decompress plan: one per chunk, written by k_plan_decode from the chunk's own header.
 struct DInfo {
   int32_t nbytes, blocksize, cbytes, nblocks, leftover;
-  int32_t item_base[2];  // first work item of this chunk in class 0 (lz4/blosclz/stored/special) and 1 (zstd)
-  int32_t status;        // header-level status (0 = ok)
+  int32_t item_base;     // first work item (= block) of this chunk in the batch-wide item numbering
+  int32_t nitems;        // blocks to decode (0 for chunks fully handled by the plan kernel / failed chunks)
+  int32_t vts;           // special "repeated value" chunks: size of the value (cbytes - 32)
   uint8_t version, flags, typesize, filter, fmt, dont_split, special, memcpyed, hdr, pad[3];
+};
+
+// Result of a batch, per chunk (device -> host).
+struct DResult {
+  int32_t out_bytes;
+  int32_t status;
 };
 
 // Compress plan: one per chunk, written on the host (all geometry is known there).
@@ -43,16 +59,27 @@ struct CInfo {
   int32_t item_base;
   int32_t memcpyed;      // clevel 0 or nbytes < 32: stored chunk
   int32_t dont_split;
-  int32_t status;
+  int32_t status;        // host-side validation result (0 = ok)
 };
 
 // Per-chunk running state of a compress batch (device, zero-initialised per batch).
 struct CState {
-  unsigned long long chain;  // decoupled look-back chain: (blocks_published << 32) | bytes_used
   int32_t overflow;          // some block did not fit dst_capacity -> chunk becomes memcpyed
   int32_t nonzero_streams;   // streams that are not zero runs (0 -> SPECIAL_ZERO chunk)
   int32_t done_blocks;
-  int32_t err;
+  int32_t total;             // bytes used by the chunk when every block fitted
+};
+
+// Compress parameters shared by the whole batch.
+struct CParams {
+  uint8_t codec, clevel, typesize, filter;
+};
+
+// Batch-wide counters (device).
+struct BatchCtl {
+  int32_t total_items;   // written by the plan kernel (decode) or the host (compress)
+  int32_t ticket;        // dynamic work distribution
+  int32_t pad[2];
 };
 
 __device__ __forceinline__ int32_t ld_le32(const uint8_t* p) {
@@ -62,18 +89,6 @@ __device__ __forceinline__ void st_le32(uint8_t* p, int32_t v) {
   p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24);
 }
 
-// 8 bytes from an arbitrarily aligned global address, using only aligned 8-byte loads that contain at
-// least one requested byte (never touches a word that lies wholly outside [p, p+8)).
-__device__ __forceinline__ uint64_t ldg_u64_unaligned(const uint8_t* p) {
-  uintptr_t a = (uintptr_t)p;
-  const uint64_t* w = (const uint64_t*)(a & ~(uintptr_t)7);
-  unsigned sh = (unsigned)(a & 7) * 8;
-  uint64_t lo = __ldg(w);
-  if (sh == 0) return lo;
-  uint64_t hi = __ldg(w + 1);
-  return (lo >> sh) | (hi << (64 - sh));
-}
-
 // Transpose an 8x8 bit matrix held in a u64 (byte r = row r, bit c = column c)  ->  byte c = column c.
 __device__ __forceinline__ uint64_t transpose8x8(uint64_t x) {
   uint64_t t;
@@ -81,6 +96,42 @@ __device__ __forceinline__ uint64_t transpose8x8(uint64_t x) {
   t = (x ^ (x >> 14)) & 0x0000CCCC0000CCCCull; x = x ^ t ^ (t << 14);
   t = (x ^ (x >> 28)) & 0x00000000F0F0F0F0ull; x = x ^ t ^ (t << 28);
   return x;
+}
+
+__device__ __forceinline__ int lane_id() { return (int)(threadIdx.x & 31); }
+__device__ __forceinline__ int warp_id() { return (int)(threadIdx.x >> 5); }
+
+// Dynamic shared memory base of the running CTA.
+#ifdef B2G_SIM
+__device__ __forceinline__ uint8_t* dyn_smem() { return cusim::S().cur->cta->smem; }
+#define B2G_SPIN_PAUSE() cusim::spin_yield()
+#else
+extern __shared__ __align__(1024) uint8_t b2g_dyn_smem_[];
+__device__ __forceinline__ uint8_t* dyn_smem() { return b2g_dyn_smem_; }
+#define B2G_SPIN_PAUSE() __nanosleep(64)
+#endif
+
+// Volatile / release-acquire accessors for cross-CTA flags.
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+#ifdef B2G_SIM
+  return *(const volatile unsigned long long*)p;
+#else
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+#endif
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
+#ifdef B2G_SIM
+  *(volatile unsigned long long*)p = v;
+#else
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+#endif
+}
+
+// Record the first error of a chunk (0 = ok, errors are negative).
+__device__ __forceinline__ void set_status(DResult* res, int chunk, int code) {
+  if (code < 0) atomicCAS(&res[chunk].status, 0, code);
 }
 
 }  // namespace b2g

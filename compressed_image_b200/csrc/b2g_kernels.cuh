@@ -1,0 +1,574 @@
+// b2g_kernels.cuh -- the batch kernels of the b2g engine (sm_100a).
+//
+//   k_plan_decode   one thread per chunk: parse + validate the blosc2 header (F1/F2/F4 of SURVEY.md 8a;
+//                   blosc/blosc2.c:672-766, 2298-2391, 2922-2951), lay the batch out as work items (= blocks).
+//   k_decode<Z>     persistent CTAs pull block items from a ticket; per block: stream directory, one warp per stream
+//                   (lz4 / blosclz / zstd / stored / run / zero: blosc_d, blosc2.c:1568-1937) into a shared-memory
+//                   window, then the fused un-filter writes the raw block with 128-bit stores (pipeline_backward,
+//                   blosc2.c:1336-1461).  <Z = true> adds the zstd work areas and serves only zstd chunks.
+//   k_compress      persistent CTAs, ticket order: fused filter into the shared window (pipeline_forward,
+//                   blosc2.c:940-1050), one warp per stream (run detection blosc2.c:1054-1076, lz4 / blosclz, raw
+//                   fallback: blosc_c, blosc2.c:1080-1332) into an L2-resident per-CTA slab, decoupled look-back over
+//                   the chunk's blocks for the output offset, compaction into the chunk with bstarts.
+//   k_finalize      chunk headers, SPECIAL_ZERO and memcpyed fallbacks (blosc2.c:2393-2529).
+//   k_filter        standalone filters (K1-K4).
+#pragma once
+#include "b2g_blosclz.cuh"
+#include "b2g_filters.cuh"
+#include "b2g_zstd.cuh"
+
+namespace b2g {
+
+// ---- decode plan ---------------------------------------------------------------------------------------------------
+struct PlanArgs {
+  const DChunk* chunks;
+  DInfo* info;
+  DResult* res;
+  int32_t* base;       // [2][n + 1] exclusive item offsets per class (0 = lz4/blosclz/stored/special, 1 = zstd)
+  BatchCtl* ctl;       // [2]
+  int32_t n;
+  int32_t max_block;   // largest blocksize the decode kernels can take (window or scratch slab)
+  int32_t zstd_ok;     // the zstd kernel will be launched
+};
+
+__device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_block, int zstd_ok) {
+  const uint8_t* src = ch.src;
+  const int32_t srcsize = ch.src_bytes;
+  d.nitems = 0; d.nblocks = 0; d.nbytes = 0; d.vts = 0;
+  if (srcsize < kHdrMin) return kErrRead;
+  d.version = src[0];
+  d.flags = src[2];
+  d.typesize = src[3];
+  const int32_t nbytes = ld_le32(src + 4), blocksize = ld_le32(src + 8), cbytes = ld_le32(src + 12);
+  d.blocksize = blocksize; d.cbytes = cbytes;
+  if (d.version > 5) return kErrVersion;
+  if (cbytes < kHdrMin) return kErrHeader;
+  if (blocksize <= 0 || (nbytes > 0 && blocksize > nbytes)) return kErrHeader;
+  if (blocksize > kMaxBlocksize) return kErrHeader;
+  if (d.typesize == 0) return kErrHeader;
+  const int ts = d.typesize;
+  const bool ext = (d.flags & kFlagShuffle) && (d.flags & kFlagBitshuffle);
+  d.hdr = ext ? kHdrExt : kHdrMin;
+  d.filter = kFilterNone;
+  d.special = 0;
+  uint8_t b2flags = 0;
+  if (ext) {
+    if (cbytes < kHdrExt) return kErrHeader;
+    if (srcsize < kHdrExt) return kErrRead;
+    b2flags = src[31];
+    d.special = (b2flags >> 4) & 7;
+    if (d.special == 3) {
+      int32_t vts = cbytes - kHdrExt;
+      if (vts <= 0 || vts > nbytes || nbytes % vts) return kErrHeader;
+      d.vts = vts;
+    } else if (d.special != 0) {
+      if (nbytes % ts) return kErrHeader;
+    }
+    for (int i = 0; i < 6; i++) {
+      uint8_t f = src[16 + i];
+      if (d.version == 4 && i == 5) f = 0;  // alpha series (blosc2.c:758-761)
+      if (f == 0) continue;
+      if ((f == kFilterShuffle || f == kFilterBitshuffle) && d.filter == kFilterNone) d.filter = f;
+      else return kErrFilter;
+    }
+  } else {
+    if (d.flags & kFlagDelta) return kErrFilter;
+    if (d.flags & kFlagShuffle) d.filter = kFilterShuffle;
+    if (d.flags & kFlagBitshuffle) d.filter = kFilterBitshuffle;
+  }
+  if (nbytes > ch.dst_cap) return kErrWrite;
+  if (cbytes > srcsize) return kErrHeader;
+  if (d.special > 4) return kErrData;
+  d.memcpyed = (d.flags & kFlagMemcpyed) ? 1 : 0;
+  if (d.memcpyed && cbytes != nbytes + d.hdr) return kErrData;
+  d.nbytes = nbytes;
+  if (nbytes == 0 && cbytes == d.hdr && !d.special) return 0;
+  if (ext && (b2flags & 0x08) && !d.special) return kErrParam;
+  if (ext && (b2flags & 0x01)) return kErrCodec;
+  if (d.special == 2 && ts != 4 && ts != 8) return kErrData;
+  int32_t nblocks = nbytes / blocksize;
+  d.leftover = nbytes % blocksize;
+  if (d.leftover > 0) nblocks++;
+  d.nblocks = nblocks;
+  d.fmt = d.flags >> 5;
+  d.dont_split = (d.flags & kFlagDontSplit) >> 4;
+  if (!d.special && !d.memcpyed) {
+    if (srcsize < d.hdr + 4 * nblocks) return kErrRead;
+    if (d.fmt != kFmtBlosclz && d.fmt != kFmtLz4 && d.fmt != kFmtZstd) return kErrCodec;
+    if (blocksize > max_block) return kErrBlocksize;
+    if (d.fmt == kFmtZstd && !zstd_ok) return kErrCtxCodec;
+  }
+  d.nitems = nblocks;
+  return 0;
+}
+
+__global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
+  int32_t* cnt = (int32_t*)dyn_smem();  // [2][blockDim.x] partial sums
+  const int t = (int)threadIdx.x, nt = (int)blockDim.x;
+  const int per = (a.n + nt - 1) / nt;
+  const int lo = min(a.n, t * per), hi = min(a.n, lo + per);
+  int32_t sum[2] = {0, 0};
+  for (int i = lo; i < hi; i++) {
+    DInfo d;
+    int rc = plan_one(a.chunks[i], d, a.max_block, a.zstd_ok);
+    if (rc < 0) d.nitems = 0;
+    a.res[i].status = rc;
+    a.res[i].out_bytes = rc < 0 ? 0 : d.nbytes;
+    const int cls = (d.nitems > 0 && !d.special && !d.memcpyed && d.fmt == kFmtZstd) ? 1 : 0;
+    d.pad[0] = (uint8_t)cls;
+    d.item_base = sum[cls];  // provisional: offset inside this thread's range
+    sum[cls] += d.nitems;
+    a.info[i] = d;
+  }
+  cnt[t] = sum[0];
+  cnt[nt + t] = sum[1];
+  __syncthreads();
+  if (t == 0) {  // serial scan over <= 1024 partials
+    for (int k = 0; k < 2; k++) {
+      int32_t run = 0;
+      for (int i = 0; i < nt; i++) { int32_t v = cnt[k * nt + i]; cnt[k * nt + i] = run; run += v; }
+      a.ctl[k].total_items = run;
+      a.ctl[k].ticket = 0;
+      a.base[k * (a.n + 1) + a.n] = run;
+    }
+  }
+  __syncthreads();
+  int32_t off[2] = {cnt[t], cnt[nt + t]};
+  for (int i = lo; i < hi; i++) {
+    const int cls = a.info[i].pad[0];
+    const int32_t nit = a.info[i].nitems;
+    a.base[i] = off[0];
+    a.base[(a.n + 1) + i] = off[1];
+    a.info[i].item_base = off[cls];
+    off[cls] += nit;
+  }
+}
+
+// Work item -> chunk: largest c with base[c] <= item (chunks without items have empty ranges).  Tickets grow
+// monotonically per CTA, so gallop forward from the previous answer, then bisect.
+__device__ __forceinline__ int find_chunk(const int32_t* base, int n, int item, int hint) {
+  int lo = hint, step = 1;
+  int hi = lo + 1;
+  while (hi < n && base[hi] <= item) { lo = hi; hi += step; step <<= 1; }
+  if (hi > n) hi = n;
+  // invariant: base[lo] <= item, and (hi == n or base[hi] > item)
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (base[mid] <= item) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// ---- decode ----------------------------------------------------------------------------------------------------------
+struct DecodeArgs {
+  const DChunk* chunks;
+  const DInfo* info;
+  DResult* res;
+  const int32_t* base;   // this class's [n + 1]
+  BatchCtl* ctl;         // this class's
+  int32_t n;
+  int32_t win_bytes;     // shared-memory window capacity
+  uint8_t* slab;         // global scratch for blocks larger than the window: one slab per CTA
+  int64_t slab_stride;
+};
+
+struct DecodeShared {
+  int32_t item, chunk;
+  int32_t spos[kMaxStreams];    // payload offset of each stream inside the chunk
+  int32_t scsize[kMaxStreams];  // its csize field
+  int32_t err;
+};
+
+// One stream of a block (blosc2.c:1783-1923) decoded by one warp into out[0..neblock).
+template <bool Z>
+__device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, int32_t csize, int32_t avail,
+                                             uint8_t* out, int32_t neblock, ZWork* zw) {
+  const int lane = lane_id();
+  if (csize == 0) {
+    fill_bytes(out, 0, neblock, lane, 32);
+    return 0;
+  }
+  if (csize < 0) {
+    if (avail < 1) return kErrRead;
+    const uint8_t token = payload[0];
+    if (!(token & 1)) return kErrRunLength;
+    if (csize < -255) return kErrRunLength;
+    fill_bytes(out, (uint8_t)(-csize), neblock, lane, 32);
+    return 0;
+  }
+  if (csize > avail) return kErrRead;
+  if (csize == neblock) {
+    copy_bytes(out, payload, neblock, lane, 32);
+    return 0;
+  }
+  int got;
+  if (Z) {
+    if (fmt != kFmtZstd) return kErrCodec;
+    long r = zstd_decode_warp(zw, payload, csize, out, neblock);
+    got = r < 0 ? 0 : (int)r;  // blosc2.c:545-548: zstd errors surface as 0 bytes
+  } else {
+    if (fmt == kFmtLz4) got = lz4_decode_warp(payload, csize, out, neblock);
+    else if (fmt == kFmtBlosclz) got = blosclz_decode_warp(payload, csize, out, neblock);
+    else return kErrCodec;
+  }
+  return got == neblock ? 0 : kErrData;
+}
+
+template <bool Z>
+__global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
+  uint8_t* smem = dyn_smem();
+  uint8_t* win_s = smem;                                       // [win_bytes]
+  DecodeShared* sh = (DecodeShared*)(smem + a.win_bytes);      // win_bytes is a multiple of 16
+  ZWork* zwork = (ZWork*)(smem + a.win_bytes + 256);           // [kCtaWarps] when Z
+  const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
+  int hint = 0;
+  for (;;) {
+    __syncthreads();  // previous item fully retired (window + sh reusable)
+    if (tid == 0) {
+      int item = atomicAdd(&a.ctl->ticket, 1);
+      int c = -1;
+      if (item < a.ctl->total_items) c = find_chunk(a.base, a.n, item, hint);
+      sh->item = item;
+      sh->chunk = c;
+      sh->err = 0;
+    }
+    __syncthreads();
+    const int c = sh->chunk;
+    if (c < 0) break;
+    hint = c;
+    const int item = sh->item;
+    const DInfo d = a.info[c];
+    const DChunk ch = a.chunks[c];
+    const int j = item - d.item_base;
+    const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
+    const int32_t bsize = is_left ? d.leftover : d.blocksize;
+    uint8_t* raw = ch.dst + (size_t)j * d.blocksize;
+
+    if (d.special) {  // blosc2.c:1694-1718
+      if (d.special == 1 || d.special == 4) {
+        fill_bytes(raw, 0, bsize, tid, kCtaThreads);  // 4 = uninitialised: any content is legal, zeros are stable
+      } else if (d.special == 2) {
+        if (d.typesize == 4) {
+          for (int i = tid; i < bsize / 4; i += kCtaThreads) st_le32(raw + 4 * i, 0x7fc00000);
+        } else {
+          for (int i = tid; i < bsize / 8; i += kCtaThreads) { st_le32(raw + 8 * i, 0); st_le32(raw + 8 * i + 4, 0x7ff80000); }
+        }
+      } else {
+        const size_t o = (size_t)j * d.blocksize;
+        for (int i = tid; i < bsize; i += kCtaThreads) raw[i] = ch.src[kHdrExt + (o + i) % d.vts];
+      }
+      continue;
+    }
+    if (d.memcpyed) {
+      copy_bytes(raw, ch.src + d.hdr + (size_t)j * d.blocksize, bsize, tid, kCtaThreads);
+      continue;
+    }
+
+    const int nstreams = (!d.dont_split && !is_left) ? d.typesize : 1;
+    const int32_t neblock = bsize / nstreams;
+    const int32_t srcsize = min(ch.src_bytes, d.cbytes);
+    // stream directory (serial: each csize tells where the next stream starts)
+    if (tid == 0) {
+      int err = 0;
+      const int32_t off = ld_le32(ch.src + d.hdr + 4 * j);
+      if (off <= 0 || off >= srcsize) err = kErrData;
+      if (neblock == 0) err = kErrWrite;
+      if (nstreams > kMaxStreams) err = kErrData;
+      int32_t pos = off;
+      for (int s = 0; s < nstreams && !err; s++) {
+        if (srcsize - pos < 4) { err = kErrRead; break; }
+        const int32_t cs = ld_le32(ch.src + pos);
+        pos += 4;
+        sh->spos[s] = pos;
+        sh->scsize[s] = cs;
+        if (cs > 0) {
+          if (srcsize - pos < cs) { err = kErrRead; break; }
+          pos += cs;
+        } else if (cs < 0) {
+          if (srcsize - pos < 1) { err = kErrRead; break; }
+          pos += 1;
+        }
+      }
+      sh->err = err;
+    }
+    __syncthreads();
+    if (sh->err) {
+      if (tid == 0) set_status(a.res, c, sh->err);
+      continue;
+    }
+    const bool direct = d.filter == kFilterNone;
+    uint8_t* win = direct ? raw
+                          : (bsize <= a.win_bytes ? win_s : a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride);
+    for (int s = warp; s < nstreams; s += kCtaWarps) {
+      const int32_t pos = sh->spos[s];
+      int rc = decode_stream<Z>(d.fmt, ch.src + pos, sh->scsize[s], srcsize - pos, win + (size_t)s * neblock,
+                                neblock, Z ? zwork + warp : nullptr);
+      if (rc < 0 && lane == 0) atomicCAS(&sh->err, 0, rc);
+    }
+    __syncthreads();
+    if (sh->err) {
+      if (tid == 0) set_status(a.res, c, sh->err);
+      continue;
+    }
+    if (!direct) filter_backward(d.filter, d.typesize, bsize, win, raw, d.version, tid, kCtaThreads);
+  }
+}
+
+// ---- compress --------------------------------------------------------------------------------------------------------
+struct CompressArgs {
+  const DChunk* chunks;          // src = raw elements, dst = chunk out
+  const CInfo* info;
+  CState* state;
+  const int32_t* base;           // [n + 1]
+  BatchCtl* ctl;
+  unsigned long long* desc;      // [total_items] look-back descriptors, zeroed per batch
+  uint8_t* slab;                 // per-CTA scratch for compressed streams
+  int64_t slab_stride;
+  int32_t n;
+  int32_t win_bytes;
+  int32_t htab_bytes;            // shared hash-table region: each active warp gets (1 << hlog) uint16 entries, hlog
+                                 // chosen per block so that a stream of neblock bytes owns neblock / 2 table bytes
+  CParams p;
+};
+
+struct CompressShared {
+  int32_t item, chunk;
+  int32_t psize[kMaxStreams];   // payload bytes of each stream (0 or 1 for zero / run streams)
+  int32_t csize[kMaxStreams];   // csize field as written
+  int32_t raw[kMaxStreams];     // payload is the raw window (stored stream)
+  int32_t offset;               // byte offset of this block inside the chunk
+};
+
+constexpr unsigned long long kDescAggregate = 1ull << 62, kDescInclusive = 2ull << 62, kDescMask = (1ull << 62) - 1;
+
+// Is in[0..n) one repeated byte?  (get_run, blosc2.c:1054-1076)
+__device__ __forceinline__ bool warp_is_run(const uint8_t* in, int n, int lane) {
+  const uint8_t v = in[0];
+  bool same = true;
+  if ((((uintptr_t)in) & 15) == 0) {
+    const uint32_t w = 0x01010101u * v;
+    const uint4* p = (const uint4*)in;
+    const int groups = n >> 4;
+    for (int g = lane; g < groups && same; g += 32) {
+      uint4 x = p[g];
+      same = (x.x == w) && (x.y == w) && (x.z == w) && (x.w == w);
+    }
+    for (int i = (groups << 4) + lane; i < n; i += 32) same = same && in[i] == v;
+  } else {
+    for (int i = lane; i < n && same; i += 32) same = in[i] == v;
+  }
+  return __all_sync(kFull, same);
+}
+
+__global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
+  uint8_t* smem = dyn_smem();
+  uint8_t* win = smem;                                            // [win_bytes] filtered block
+  uint16_t* htabs = (uint16_t*)(smem + a.win_bytes);              // [kCtaWarps][1 << hlog]
+  CompressShared* sh = (CompressShared*)(smem + a.win_bytes + a.htab_bytes);
+  const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
+  uint8_t* slab = a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride;
+  int hint = 0;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) {
+      int item = atomicAdd(&a.ctl->ticket, 1);
+      int c = -1;
+      if (item < a.ctl->total_items) c = find_chunk(a.base, a.n, item, hint);
+      sh->item = item;
+      sh->chunk = c;
+    }
+    __syncthreads();
+    const int c = sh->chunk;
+    if (c < 0) break;
+    hint = c;
+    const int item = sh->item;
+    const CInfo d = a.info[c];
+    const int j = item - d.item_base;
+    if (d.status < 0 || d.memcpyed || j >= d.nblocks) continue;  // k_finalize stores these chunks
+    const DChunk ch = a.chunks[c];
+    const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
+    const int32_t bsize = is_left ? d.leftover : d.blocksize;
+    const int ts = a.p.typesize;
+    filter_forward(a.p.filter, ts, bsize, ch.src + (size_t)j * d.blocksize, win, tid, kCtaThreads);
+    __syncthreads();
+    const int nstreams = (!d.dont_split && !is_left) ? ts : 1;
+    const int32_t neblock = bsize / nstreams;
+    const int32_t sstride = (neblock + 15) & ~15;  // slab region per stream
+    int hlog = 29 - __clz(neblock);                // floor(log2(neblock)) - 2: table bytes <= neblock / 2
+    hlog = hlog < 6 ? 6 : (hlog > 13 ? 13 : hlog);
+    uint16_t* htab = htabs + ((size_t)warp << hlog);
+    for (int s = warp; s < nstreams; s += kCtaWarps) {
+      const uint8_t* in = win + (size_t)s * neblock;
+      uint8_t* out = slab + (size_t)s * sstride;
+      int32_t psize, csize, raw = 0;
+      if (warp_is_run(in, neblock, lane)) {
+        const uint8_t v = in[0];
+        csize = -(int32_t)v;
+        psize = v ? 1 : 0;
+        if (lane == 0 && v) out[0] = 0x01;
+      } else {
+        int r = 0;
+        const int cap = neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
+        if (a.p.codec == kCodecLz4) r = lz4_encode_warp(in, neblock, out, cap, htab, hlog);
+        else r = blosclz_encode_warp(in, neblock, out, cap, htab, hlog);
+        if (r <= 0 || r >= neblock) { raw = 1; psize = csize = neblock; }
+        else psize = csize = r;
+      }
+      if (lane == 0) { sh->psize[s] = psize; sh->csize[s] = csize; sh->raw[s] = raw; }
+    }
+    __syncthreads();
+    // block size + decoupled look-back over the earlier blocks of this chunk (warp 0)
+    if (warp == 0) {
+      int32_t total = 0, nonzero = 0;
+      for (int s = 0; s < nstreams; s++) { total += 4 + sh->psize[s]; nonzero += sh->csize[s] != 0; }
+      const int first = d.item_base;
+      unsigned long long prefix = 0;
+      if (item > first) {
+        if (lane == 0) st_release_u64(&a.desc[item], kDescAggregate | (unsigned long long)total);
+        int look = item - 1;
+        for (;;) {
+          const int idx = look - lane;
+          unsigned long long v = kDescInclusive;  // lanes before the chunk start act as a zero inclusive prefix
+          if (idx >= first) {
+            for (;;) {
+              v = ld_acquire_u64(&a.desc[idx]);
+              if (v >> 62) break;
+              B2G_SPIN_PAUSE();
+            }
+          }
+          const unsigned inc = __ballot_sync(kFull, (v >> 62) == 2);
+          const int stop = inc ? __ffs((int)inc) - 1 : 31;
+          unsigned long long part = lane <= stop ? (v & kDescMask) : 0ull;
+          for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
+          prefix += part;
+          if (inc) break;
+          look -= 32;
+        }
+      }
+      if (lane == 0) {
+        st_release_u64(&a.desc[item], kDescInclusive | (prefix + (unsigned long long)total));
+        const int32_t off = kHdrExt + 4 * d.nblocks + (int32_t)prefix;
+        const int32_t limit = min(ch.dst_cap, d.nbytes + kHdrExt);
+        if (off + total > limit) {
+          atomicExch(&a.state[c].overflow, 1);
+          sh->offset = -1;
+        } else {
+          sh->offset = off;
+          st_le32(ch.dst + kHdrExt + 4 * j, off);
+        }
+        if (nonzero) atomicAdd(&a.state[c].nonzero_streams, nonzero);
+        if (j == d.nblocks - 1) a.state[c].total = kHdrExt + 4 * d.nblocks + (int32_t)prefix + total;
+      }
+    }
+    __syncthreads();
+    int32_t off = sh->offset;
+    if (off < 0) continue;
+    // compaction: [csize][payload] per stream, in order
+    for (int s = 0; s < nstreams; s++) {
+      const int32_t ps = sh->psize[s];
+      uint8_t* o = ch.dst + off;
+      if (tid == 0) st_le32(o, sh->csize[s]);
+      const uint8_t* from = sh->raw[s] ? win + (size_t)s * neblock : slab + (size_t)s * sstride;
+      copy_bytes(o + 4, from, ps, tid, kCtaThreads);
+      off += 4 + ps;
+    }
+  }
+}
+
+struct FinalizeArgs {
+  const DChunk* chunks;
+  const CInfo* info;
+  const CState* state;
+  DResult* res;
+  const int32_t* base;
+  int32_t n;
+  int32_t total_items;
+  CParams p;
+};
+
+// One CTA per work item (block): chunk header by the chunk's first item, raw copy of every block of a memcpyed chunk.
+__global__ void __launch_bounds__(kCtaThreads) k_finalize(FinalizeArgs a) {
+  const int tid = (int)threadIdx.x;
+  for (int item = (int)blockIdx.x; item < a.total_items; item += (int)gridDim.x) {
+    const int c = find_chunk(a.base, a.n, item, 0);
+    const CInfo d = a.info[c];
+    const DChunk ch = a.chunks[c];
+    const int j = item - d.item_base;
+    if (d.status < 0) {
+      if (j == 0 && tid == 0) { a.res[c].status = d.status; a.res[c].out_bytes = 0; }
+      continue;
+    }
+    const CState st = a.state[c];
+    const bool stored = d.memcpyed || st.overflow;
+    const bool fits = !stored || d.nbytes + kHdrExt <= ch.dst_cap;
+    if (j == 0 && tid == 0) {
+      uint8_t* h = ch.dst;
+      int32_t cbytes = 0;
+      if (fits) {
+        uint8_t flags = kFlagShuffle | kFlagBitshuffle;  // both bits = "extended header" marker (blosc2.c:2413)
+        uint8_t b2flags = 0;
+        if (!d.memcpyed) {
+          const uint8_t fmt = a.p.codec == kCodecBlosclz ? kFmtBlosclz : kFmtLz4;
+          flags |= (uint8_t)(d.dont_split << 4) | (uint8_t)(fmt << 5);
+        }
+        if (stored) {
+          flags |= kFlagMemcpyed;
+          cbytes = d.nbytes + kHdrExt;
+        } else if (st.nonzero_streams == 0) {
+          b2flags = 1 << 4;  // BLOSC2_SPECIAL_ZERO (blosc2.c:2520-2529)
+          cbytes = kHdrExt;
+        } else {
+          cbytes = st.total;
+        }
+        for (int i = 0; i < kHdrExt; i++) h[i] = 0;
+        h[0] = 5;  // BLOSC2_VERSION_FORMAT_STABLE
+        h[1] = 1;
+        h[2] = flags;
+        h[3] = a.p.typesize;
+        st_le32(h + 4, d.nbytes);
+        st_le32(h + 8, d.blocksize);
+        st_le32(h + 12, cbytes);
+        h[16 + 5] = a.p.filter;
+        h[22] = a.p.codec;
+        h[31] = b2flags;
+      }
+      a.res[c].status = 0;
+      a.res[c].out_bytes = cbytes;  // 0 = does not fit, like blosc2_compress_ctx returning 0
+    }
+    if (stored && fits && j < d.nblocks) {
+      const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
+      const int32_t bsize = is_left ? d.leftover : d.blocksize;
+      copy_bytes(ch.dst + kHdrExt + (size_t)j * d.blocksize, ch.src + (size_t)j * d.blocksize, bsize, tid,
+                 kCtaThreads);
+    }
+  }
+}
+
+// ---- standalone filters ------------------------------------------------------------------------------------------
+struct FilterArgs {
+  const uint8_t* src;
+  uint8_t* dst;
+  int64_t n;
+  int32_t blocksize, typesize, filter, forward, version, nblocks;
+};
+
+__global__ void __launch_bounds__(kCtaThreads) k_filter(FilterArgs a) {
+  uint8_t* win = dyn_smem();
+  const int tid = (int)threadIdx.x;
+  for (int b = (int)blockIdx.x; b < a.nblocks; b += (int)gridDim.x) {
+    const int64_t o = (int64_t)b * a.blocksize;
+    const int32_t bsize = (int32_t)min((int64_t)a.blocksize, a.n - o);
+    __syncthreads();
+    if (a.forward) {
+      filter_forward(a.filter, a.typesize, bsize, a.src + o, win, tid, kCtaThreads);
+      __syncthreads();
+      copy_bytes(a.dst + o, win, bsize, tid, kCtaThreads);
+    } else {
+      copy_bytes(win, a.src + o, bsize, tid, kCtaThreads);
+      __syncthreads();
+      filter_backward(a.filter, a.typesize, bsize, win, a.dst + o, a.version, tid, kCtaThreads);
+    }
+  }
+}
+
+}  // namespace b2g

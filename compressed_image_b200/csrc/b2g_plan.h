@@ -1,0 +1,51 @@
+// b2g_plan.h -- host-side compress planning (pure C++, shared by b2g_api.cu and the test simulator).
+// Restates the geometry rules of c-blosc2 that the reference reaches through blosc2_compress_ctx:
+//   blocksize   blosc/stune.c:46-164  (a user blocksize wins; clamp to nbytes; multiple of typesize)
+//   split rule  blosc/stune.c:185-210 (BLOSC_AUTO_SPLIT, the only mode compressed-image uses: wrapper.h:352)
+//   memcpyed    blosc/blosc2.c:2400-2407 (clevel 0 or nbytes < 32)
+#pragma once
+#include <algorithm>
+#include <climits>
+#include <cstring>
+
+#include "b2g_dev.cuh"
+
+namespace b2g {
+
+inline bool plan_split_block(int codec, int clevel, int filter, int typesize, int blocksize) {
+  return ((codec == kCodecBlosclz || codec == kCodecLz4 || (codec == kCodecZstd && clevel <= 5)) &&
+          filter == kFilterShuffle && typesize <= kMaxStreams && (blocksize / typesize) >= kMinBuffer);
+}
+
+inline int plan_blocksize(int user, int typesize, int nbytes) {
+  int bs = user > 0 ? user : 32768;
+  if (nbytes < typesize) return 1;
+  if (bs > nbytes) bs = nbytes;
+  if (bs > typesize) bs = bs / typesize * typesize;
+  return std::max(bs, 1);
+}
+
+// Fills one CInfo; returns the number of work items the chunk occupies (>= 1 so that every chunk gets a header).
+inline int plan_compress_chunk(CInfo& d, const CParams& p, int user_blocksize, int32_t nbytes, int32_t dst_cap,
+                               int win_bytes) {
+  memset(&d, 0, sizeof(d));
+  d.nbytes = nbytes;
+  if (nbytes < 0 || nbytes > INT32_MAX - kHdrExt) d.status = kErrMaxBuf;
+  else if (dst_cap < kHdrExt) d.status = kErrMaxBuf;
+  if (d.status == 0) {
+    d.blocksize = plan_blocksize(user_blocksize, p.typesize, nbytes);
+    d.nblocks = nbytes / d.blocksize;
+    d.leftover = nbytes % d.blocksize;
+    if (d.leftover > 0) d.nblocks++;
+    d.memcpyed = (p.clevel == 0 || nbytes < kMinBuffer) ? 1 : 0;
+    d.dont_split = plan_split_block(p.codec, p.clevel, p.filter, p.typesize, d.blocksize) ? 0 : 1;
+    if (!d.memcpyed && d.blocksize > win_bytes) d.status = kErrBlocksize;  // the encoder window is shared memory
+  }
+  return std::max(d.nblocks, 1);
+}
+
+// Shared hash-table region of the encoder for a given window: half the window (see k_compress), at least 4 x 64
+// entries, at most 4 x 8192 entries.
+inline int plan_htab_bytes(int win_bytes) { return std::min(std::max(win_bytes / 2, 1024), 4 * 16384); }
+
+}  // namespace b2g

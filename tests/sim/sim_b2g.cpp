@@ -1,0 +1,146 @@
+// sim_b2g.cpp -- TEST INFRASTRUCTURE ONLY.  Runs the product's device code (compressed_image_b200/csrc/*.cuh,
+// unmodified) on the CPU under tests/sim/cusim.h and exposes flat entry points for the ctypes tests.  The host
+// orchestration mirrors b2g_api.cu (plan -> decode kernels; host plan -> compress -> finalize) on plain host arrays.
+#include "cusim.h"
+
+#include "../../compressed_image_b200/csrc/b2g_kernels.cuh"
+#include "../../compressed_image_b200/csrc/b2g_plan.h"
+
+using namespace b2g;
+
+static size_t au(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" {
+
+// Decompress a batch.  grid = number of simulated persistent CTAs; win_bytes = shared window (blocks above it use
+// the slab path).  out[i] = nbytes or 0, status[i] = 0 or error.
+int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes, void* const* dsts,
+                         const int32_t* caps, int32_t* out, int32_t* status, int win_bytes, int max_block, int grid,
+                         int zstd_ok) {
+  std::vector<DChunk> ch(n);
+  std::vector<DInfo> info(n);
+  std::vector<DResult> res(n);
+  std::vector<int32_t> base(2 * (n + 1));
+  BatchCtl ctl[2];
+  memset(ctl, 0, sizeof(ctl));
+  for (int i = 0; i < n; i++) {
+    ch[i].src = (const uint8_t*)srcs[i];
+    ch[i].dst = (uint8_t*)dsts[i];
+    ch[i].src_bytes = srcsizes[i];
+    ch[i].dst_cap = caps[i];
+  }
+  win_bytes = (int)au(win_bytes, 16);
+  PlanArgs pa;
+  pa.chunks = ch.data(); pa.info = info.data(); pa.res = res.data(); pa.base = base.data(); pa.ctl = ctl;
+  pa.n = n; pa.max_block = max_block; pa.zstd_ok = zstd_ok;
+  cusim::launch(dim3(1), dim3(1024), 2 * 1024 * sizeof(int32_t), [&] { k_plan_decode(pa); });
+  const size_t stride = au((size_t)max_block + 512, 256);
+  std::vector<uint8_t> slab(stride * grid + 256);
+  DecodeArgs da;
+  da.chunks = ch.data(); da.info = info.data(); da.res = res.data(); da.base = base.data(); da.ctl = &ctl[0];
+  da.n = n; da.win_bytes = win_bytes; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
+  cusim::launch(dim3(grid), dim3(kCtaThreads), (size_t)win_bytes + 256, [&] { k_decode<false>(da); });
+  if (zstd_ok) {
+    da.base = base.data() + (n + 1);
+    da.ctl = &ctl[1];
+    cusim::launch(dim3(grid), dim3(kCtaThreads), (size_t)win_bytes + 256 + sizeof(ZWork) * kCtaWarps,
+                  [&] { k_decode<true>(da); });
+  }
+  for (int i = 0; i < n; i++) {
+    status[i] = res[i].status;
+    out[i] = res[i].status < 0 ? 0 : res[i].out_bytes;
+  }
+  return 0;
+}
+
+int sim_compress_batch(int codec, int clevel, int typesize, int filter, int blocksize, int n,
+                       const void* const* srcs, const int32_t* nbytes, void* const* dsts, const int32_t* caps,
+                       int32_t* out, int32_t* status, int win_bytes, int grid, int hlog) {
+  std::vector<DChunk> ch(n);
+  std::vector<CInfo> info(n);
+  std::vector<CState> state(n);
+  std::vector<DResult> res(n);
+  std::vector<int32_t> base(n + 1);
+  memset(state.data(), 0, sizeof(CState) * n);
+  CParams p;
+  p.codec = (uint8_t)codec; p.clevel = (uint8_t)clevel; p.typesize = (uint8_t)typesize; p.filter = (uint8_t)filter;
+  win_bytes = (int)au(win_bytes, 16);
+  int64_t items = 0;
+  for (int i = 0; i < n; i++) {
+    ch[i].src = (const uint8_t*)srcs[i];
+    ch[i].dst = (uint8_t*)dsts[i];
+    ch[i].src_bytes = nbytes[i];
+    ch[i].dst_cap = caps[i];
+    int nit = plan_compress_chunk(info[i], p, blocksize, nbytes[i], caps[i], win_bytes);
+    info[i].item_base = (int32_t)items;
+    base[i] = (int32_t)items;
+    items += nit;
+  }
+  base[n] = (int32_t)items;
+  BatchCtl ctl[2];
+  memset(ctl, 0, sizeof(ctl));
+  ctl[0].total_items = (int32_t)items;
+  std::vector<unsigned long long> desc(items + 1, 0ull);
+  const size_t stride = au((size_t)win_bytes + 16 * kMaxStreams + 256, 256);
+  std::vector<uint8_t> slab(stride * grid + 256);
+  CompressArgs ca;
+  ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
+  ca.desc = desc.data(); ca.slab = slab.data(); ca.slab_stride = (int64_t)stride; ca.n = n;
+  ca.win_bytes = win_bytes; ca.htab_bytes = plan_htab_bytes(win_bytes); ca.p = p;
+  const size_t smem = (size_t)win_bytes + (size_t)plan_htab_bytes(win_bytes) + 256;
+  (void)hlog;
+  cusim::launch(dim3(grid), dim3(kCtaThreads), smem, [&] { k_compress(ca); });
+  FinalizeArgs fa;
+  fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.res = res.data(); fa.base = base.data();
+  fa.n = n; fa.total_items = (int32_t)items; fa.p = p;
+  cusim::launch(dim3(std::min<int>(grid, (int)items)), dim3(kCtaThreads), 0, [&] { k_finalize(fa); });
+  for (int i = 0; i < n; i++) {
+    status[i] = res[i].status;
+    out[i] = res[i].status < 0 ? 0 : res[i].out_bytes;
+  }
+  return 0;
+}
+
+int sim_filter(int filter, int forward, int typesize, int version, const void* src, void* dst, int64_t n,
+               int blocksize, int grid) {
+  FilterArgs fa;
+  fa.src = (const uint8_t*)src; fa.dst = (uint8_t*)dst; fa.n = n; fa.blocksize = blocksize; fa.typesize = typesize;
+  fa.filter = filter; fa.forward = forward; fa.version = version;
+  fa.nblocks = (int32_t)((n + blocksize - 1) / blocksize);
+  if (fa.nblocks == 0) return 0;
+  cusim::launch(dim3(std::min(grid, fa.nblocks)), dim3(kCtaThreads), au(blocksize, 16) + 64, [&] { k_filter(fa); });
+  return 0;
+}
+
+// Raw stream codecs (one warp), for focused tests.
+int sim_stream_decode(int fmt, const void* src, int n, void* dst, int cap) {
+  int result = 0;
+  cusim::launch(dim3(1), dim3(32), sizeof(ZWork) + 64, [&] {
+    int r;
+    if (fmt == kFmtLz4) r = lz4_decode_warp((const uint8_t*)src, n, (uint8_t*)dst, cap);
+    else if (fmt == kFmtBlosclz) r = blosclz_decode_warp((const uint8_t*)src, n, (uint8_t*)dst, cap);
+    else r = (int)zstd_decode_warp((ZWork*)dyn_smem(), (const uint8_t*)src, n, (uint8_t*)dst, cap);
+    if (threadIdx.x == 0) result = r;
+  });
+  return result;
+}
+
+int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int hlog) {
+  int result = 0;
+  const size_t in_bytes = au((size_t)n + 16, 16);
+  cusim::launch(dim3(1), dim3(32), in_bytes + (2u << hlog), [&] {
+    uint8_t* in = dyn_smem();
+    for (int i = (int)threadIdx.x; i < n; i += 32) in[i] = ((const uint8_t*)src)[i];
+    __syncwarp();
+    uint16_t* ht = (uint16_t*)(in + in_bytes);
+    int r;
+    if (codec == kCodecLz4) r = lz4_encode_warp(in, n, (uint8_t*)dst, cap, ht, hlog);
+    else r = blosclz_encode_warp(in, n, (uint8_t*)dst, cap, ht, hlog);
+    if (threadIdx.x == 0) result = r;
+  });
+  return result;
+}
+
+unsigned long long sim_collectives() { return cusim::S().collectives; }
+
+}  // extern "C"
