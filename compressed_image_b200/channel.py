@@ -1,0 +1,278 @@
+"""compressed.Channel -- host-side mirror of compressed::channel<T> (compressed_image/include/compressed/channel.h)
+as exposed to Python by the reference (python/bindings/wrappers/dynamic_channel.h, bind_channel.h:17-257).
+
+A channel is a list of independently compressed blosc2 chunks (scanline-aligned, 4 MiB by default).  Where the
+reference loops over chunks calling c-blosc2 once per chunk (blosc2/schunk.h:85-104, 123-141), this class hands the
+whole list to ONE batched b2g call; the chunk bytes it stores are ordinary blosc2 chunks.
+
+Same names, argument meaning and error behaviour as the reference: size mismatches raise ValueError
+(std::invalid_argument through pybind11), bad chunk indices IndexError (std::out_of_range), codec failures and
+constructor size mismatches RuntimeError (std::runtime_error).
+"""
+import numpy as np
+
+from . import _b2g
+from .enums import Codec
+
+DEFAULT_BLOCKSIZE = 32_768        # compressed::s_default_blocksize (constants.h:11)
+DEFAULT_CHUNKSIZE = 4_194_304     # compressed::s_default_chunksize (constants.h:9)
+
+# dtypes the reference binds (python/bindings/util/variant_t.h:92-103)
+_DTYPES = tuple(np.dtype(t) for t in (np.uint8, np.int8, np.uint16, np.int16, np.uint32, np.int32, np.float16,
+                                      np.float32))
+
+_ctx_pool = {}
+
+
+def _context(codec, clevel, typesize, filt, blocksize, device=-1):
+    """Contexts own device scratch + pinned staging, so they are pooled per parameter set rather than created per
+    channel / per get_chunk as the reference does with blosc2 contexts (channel.h:511-514)."""
+    key = (int(codec), int(clevel), int(typesize), int(filt), int(blocksize), int(device))
+    ctx = _ctx_pool.get(key)
+    if ctx is None:
+        ctx = _b2g.Context(*key)
+        _ctx_pool[key] = ctx
+    return ctx
+
+
+def _check_dtype(dtype):
+    dt = np.dtype(dtype)
+    if dt not in _DTYPES:
+        raise ValueError("Unsupported dtype %s" % dt)
+    return dt
+
+
+def ensure_compression_level(level):
+    """compressed::util::ensure_compression_level (util.h:86-94): clamp to 0..9."""
+    return max(0, min(9, int(level)))
+
+
+def align_chunk_to_scanlines_bytes(width, chunk_size, itemsize):
+    """compressed::util::align_chunk_to_scanlines_bytes (util.h:115-131)."""
+    lines = int(chunk_size) // itemsize // width if width > 0 else 0
+    if lines == 0:   # util.h:121-131 throws std::runtime_error
+        raise RuntimeError("Unable to align chunk size to scanlines as the size of a scanline exceeds the chunk size. "
+                           "Got a scanline size of %d x %d (sizeof(T)) while the max size of the chunks is %d"
+                           % (width, itemsize, int(chunk_size)))
+    return lines * width * itemsize
+
+
+class _Lazy:
+    """A lazy fill-value chunk (blosc2/lazyschunk.h:47-105): nbytes of one repeated element, never compressed."""
+    __slots__ = ("value", "nbytes")
+
+    def __init__(self, value, nbytes):
+        self.value = value
+        self.nbytes = nbytes
+
+
+class Channel:
+    def __init__(self, data, width, height, compression_codec=Codec.lz4, compression_level=9,
+                 block_size=DEFAULT_BLOCKSIZE, chunk_size=DEFAULT_CHUNKSIZE, *, filter=_b2g.SHUFFLE, device=-1):
+        data = np.asarray(data)
+        self._dtype = _check_dtype(data.dtype)
+        self._init_params(width, height, compression_codec, compression_level, block_size, chunk_size, filter, device)
+        if data.size != self._width * self._height:   # channel.h:113-123 throws std::runtime_error
+            raise RuntimeError("Invalid channel data passed. Expected its size to match up to width * height (%d) but "
+                             "instead got %d" % (self._width * self._height, data.size))
+        flat = np.ascontiguousarray(data).reshape(-1).view(np.uint8)
+        cb = self._chunk_bytes
+        pieces = [flat[o:o + cb] for o in range(0, flat.size, cb)]
+        self._chunks = self._ctx().compress(pieces) if pieces else []
+
+    # ---- construction helpers ------------------------------------------------------------------------------
+    def _init_params(self, width, height, codec, level, block_size, chunk_size, filt, device):
+        self._width, self._height = int(width), int(height)
+        self._codec = Codec(codec)
+        self._level = ensure_compression_level(level)
+        self._block_size = int(block_size)
+        self._filter = int(filt)
+        self._device = int(device)
+        self._nthreads = 1
+        self._chunk_size_arg = int(chunk_size)
+        self._chunk_bytes = align_chunk_to_scanlines_bytes(self._width, chunk_size, self._dtype.itemsize)
+        self._chunks = []
+
+    def _ctx(self):
+        return _context(self._codec.blosc2_id, self._level, self._dtype.itemsize, self._filter, self._block_size,
+                        self._device)
+
+    @classmethod
+    def _lazy(cls, dtype, value, width, height, codec, level, block_size, chunk_size):
+        self = cls.__new__(cls)
+        self._dtype = _check_dtype(dtype)
+        self._init_params(width, height, codec, level, block_size, chunk_size, _b2g.SHUFFLE, -1)
+        try:
+            v = np.array(value).astype(self._dtype, casting="unsafe")[()]
+        except (TypeError, ValueError):
+            raise RuntimeError("Could not convert fill_value to the target dtype.")
+        total = self._width * self._height * self._dtype.itemsize
+        cb = self._chunk_bytes
+        self._chunks = [_Lazy(v, min(cb, total - o)) for o in range(0, total, cb)]
+        return self
+
+    @staticmethod
+    def full(dtype, fill_value, width, height, compression_codec=Codec.lz4, compression_level=9,
+             block_size=DEFAULT_BLOCKSIZE, chunk_size=DEFAULT_CHUNKSIZE):
+        return Channel._lazy(dtype, fill_value, width, height, compression_codec, compression_level, block_size,
+                             chunk_size)
+
+    @staticmethod
+    def zeros(dtype, width, height, compression_codec=Codec.lz4, compression_level=9, block_size=DEFAULT_BLOCKSIZE,
+              chunk_size=DEFAULT_CHUNKSIZE):
+        return Channel._lazy(dtype, 0, width, height, compression_codec, compression_level, block_size, chunk_size)
+
+    @staticmethod
+    def full_like(other, fill_value):
+        return Channel._lazy(other._dtype, fill_value, other._width, other._height, other._codec, other._level,
+                             other._block_size, other._chunk_size_arg)
+
+    @staticmethod
+    def zeros_like(other):
+        return Channel.full_like(other, 0)
+
+    # ---- attributes ------------------------------------------------------------------------------------------
+    @property
+    def dtype(self):
+        return self._dtype
+
+    @property
+    def shape(self):
+        return (self._height, self._width)
+
+    @property
+    def width(self):
+        return self._width
+
+    @property
+    def height(self):
+        return self._height
+
+    def compression(self):
+        return self._codec
+
+    def compression_level(self):
+        return self._level
+
+    def num_chunks(self):
+        return len(self._chunks)
+
+    def _nbytes_of(self, i):
+        c = self._chunks[i]
+        return c.nbytes if isinstance(c, _Lazy) else _b2g.chunk_sizes(c)[0]
+
+    def _index(self, i):
+        i = int(i)
+        if i < 0 or i >= len(self._chunks):   # schunk_mixin.h:204-214 -> std::out_of_range
+            raise IndexError("Cannot access index %d in schunk. Total amount of chunks is %d" % (i, len(self._chunks)))
+        return i
+
+    def block_size(self):
+        """schunk_mixin.h:191-194 max_block_size: the block size the channel was created with."""
+        return self._block_size
+
+    def chunk_size(self, chunk_index=None):
+        if chunk_index is None:
+            return self._chunk_bytes   # schunk_mixin.h:156-159: m_ChunkSize, also for the last chunk
+        return self._nbytes_of(self._index(chunk_index))
+
+    def chunk_elems(self, chunk_index=None):
+        return self.chunk_size(chunk_index) // self._dtype.itemsize
+
+    def compressed_bytes(self):
+        """schunk::csize / lazy_schunk::csize (lazyschunk.h:312-327: a lazy chunk counts sizeof(T))."""
+        return sum(self._dtype.itemsize if isinstance(c, _Lazy) else int(c.size) for c in self._chunks)
+
+    def uncompressed_size(self):
+        """In ELEMENTS (channel.h:404-420)."""
+        return sum(self._nbytes_of(i) for i in range(len(self._chunks))) // self._dtype.itemsize
+
+    def update_nthreads(self, nthreads, block_size=DEFAULT_BLOCKSIZE):
+        """Kept for API compatibility (channel.h:343-348): the grid is the thread pool, so only block_size matters."""
+        self._nthreads = int(nthreads)
+        self._block_size = int(block_size)
+
+    # ---- chunk access ----------------------------------------------------------------------------------------
+    def _decode_into(self, indices, outs):
+        """Decompress chunks[indices] into the uint8 views `outs` with one batched launch (lazy chunks are fills)."""
+        real_c, real_o = [], []
+        for i, o in zip(indices, outs):
+            c = self._chunks[i]
+            if isinstance(c, _Lazy):
+                o.view(self._dtype)[:] = c.value
+            else:
+                real_c.append(c)
+                real_o.append(o)
+        if real_c:
+            self._ctx().decompress(real_c, real_o)
+
+    def get_chunk(self, chunk_index, array=None):
+        i = self._index(chunk_index)
+        n = self._nbytes_of(i) // self._dtype.itemsize
+        if array is None:
+            array = np.empty(n, dtype=self._dtype)
+        else:
+            if not isinstance(array, np.ndarray) or array.dtype != self._dtype:
+                raise ValueError("Array must have dtype matching channel element type.")
+            if array.ndim != 1:
+                raise ValueError("Array must be 1-dimensional.")
+            if array.shape[0] != n:
+                raise ValueError("Array length does not match number of chunk elements.")
+            if not array.flags.c_contiguous or not array.flags.writeable:
+                raise ValueError("Array must be contiguous and writeable.")
+        self._decode_into([i], [array.view(np.uint8)])
+        return array
+
+    def set_chunk(self, chunk_index, array):
+        array = np.asarray(array)
+        if array.ndim != 1:
+            raise ValueError("set_chunk requires a 1D numpy array")
+        if array.dtype != self._dtype:
+            raise ValueError("set_chunk requires numpy array of dtype '%s', instead got '%s'" % (self._dtype, array.dtype))
+        i = self._index(chunk_index)
+        if array.size * self._dtype.itemsize != self._nbytes_of(i):   # schunk_mixin.h:216-246 -> std::invalid_argument
+            raise ValueError("Invalid chunk size: expected %d elements, got %d" %
+                             (self._nbytes_of(i) // self._dtype.itemsize, array.size))
+        self._chunks[i] = self._ctx().compress([array])[0]
+
+    def set_chunks(self, chunk_indices, arrays):
+        """Batched set_chunk (no reference equivalent: one launch for many chunks)."""
+        idx = [self._index(i) for i in chunk_indices]
+        for i, a in zip(idx, arrays):
+            a = np.asarray(a)
+            if a.dtype != self._dtype or a.ndim != 1 or a.size * self._dtype.itemsize != self._nbytes_of(i):
+                raise ValueError("Invalid chunk passed to set_chunks")
+        for i, c in zip(idx, self._ctx().compress(list(arrays))):
+            self._chunks[i] = c
+
+    def get_decompressed(self):
+        out = np.empty(self._width * self._height, dtype=self._dtype)
+        flat = out.view(np.uint8)
+        outs, o = [], 0
+        for i in range(len(self._chunks)):
+            nb = self._nbytes_of(i)
+            outs.append(flat[o:o + nb])
+            o += nb
+        self._decode_into(range(len(self._chunks)), outs)
+        return out.reshape(self._height, self._width)
+
+    # ---- chunk iteration (iterators/iterator.h:97-141: decompress -> user modifies -> recompress) --------------
+    def __iter__(self):
+        """Yields each chunk as a writable 1-D array; modifications are recompressed when the iterator advances
+        (and at exhaustion), like compressed::channel_iterator."""
+        for i in range(len(self._chunks)):
+            buf = self.get_chunk(i)
+            before = buf.copy()
+            yield buf
+            if not np.array_equal(before.view(np.uint8), buf.view(np.uint8)):
+                self.set_chunk(i, buf)
+
+    def chunks(self):
+        """The stored chunk bytes (numpy uint8 arrays; lazy chunks are materialised as blosc2 special chunks)."""
+        out = []
+        for c in self._chunks:
+            if isinstance(c, _Lazy):
+                out.append(self._ctx().compress([np.full(c.nbytes // self._dtype.itemsize, c.value, self._dtype)])[0])
+            else:
+                out.append(c)
+        return out

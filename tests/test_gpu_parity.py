@@ -1,0 +1,239 @@
+"""Parity tests proper (-m gpu): the sm_100a kernels, called through the C ABI (include/b2g.h), against the checker
+(oracle/liboracle.so, oracle/_ref/libblosc2_ref.so when it travelled with the snapshot) and the committed golden
+fixtures.  Bit-exact throughout: this path is integer / byte work.
+
+Mirrors tests/test_sim_kernels.py (which runs the same device code on the CPU simulator) case for case."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import _data
+import _golden
+import _libs
+
+pytestmark = pytest.mark.gpu
+
+HAVE_REF = _libs.ref() is not None
+
+
+def _gpu():
+    import _gpu as g
+    return g
+
+
+def _checker_decompress(chunk):
+    if HAVE_REF:
+        return _libs.ref_decompress(chunk)
+    return _libs.oracle_decompress(chunk)
+
+
+def test_library_loaded_and_device_present():
+    from compressed_image_b200 import _b2g
+    assert _b2g.lib().b2g_device_count() >= 1
+    assert b"sm_100a" in _b2g.lib().b2g_version()
+
+
+# ---- filters ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ts", [1, 2, 3, 4, 7, 8, 12, 16, 24])
+@pytest.mark.parametrize("n,bs", [(32768, 32768), (70000, 32768), (1000, 256), (4099, 4096), (17, 64),
+                                  (1 << 20, 32768)])
+def test_filters_match_oracle(ts, n, bs):
+    g, O = _gpu(), _libs.oracle()
+    bs = max(bs // ts * ts, ts)
+    src = _data.make_data("random", n, 1, seed=ts)
+    for filt in (_data.SHUFFLE, _data.BITSHUFFLE, _data.NOFILTER):
+        exp_f = np.zeros(n, np.uint8)
+        exp_b = np.zeros(n, np.uint8)
+        for o in range(0, n, bs):
+            m = min(bs, n - o)
+            s, a, b = src[o:o + m].copy(), np.zeros(m, np.uint8), np.zeros(m, np.uint8)
+            if filt == _data.SHUFFLE:
+                O.b2o_shuffle(ts, m, _libs.ptr(s), _libs.ptr(a)); O.b2o_unshuffle(ts, m, _libs.ptr(s), _libs.ptr(b))
+            elif filt == _data.BITSHUFFLE:
+                O.b2o_bitshuffle(ts, m, _libs.ptr(s), _libs.ptr(a)); O.b2o_bitunshuffle(ts, m, _libs.ptr(s), _libs.ptr(b), 5)
+            else:
+                a[:] = s; b[:] = s
+            exp_f[o:o + m] = a; exp_b[o:o + m] = b
+        assert np.array_equal(g.run_filter(filt, True, ts, src, bs), exp_f), ("fwd", filt)
+        assert np.array_equal(g.run_filter(filt, False, ts, src, bs), exp_b), ("bwd", filt)
+    exp = np.zeros(n, np.uint8)
+    for o in range(0, n, bs):   # Blosc1 (format version 2) bit-unshuffle rule
+        m = min(bs, n - o)
+        s, b = src[o:o + m].copy(), np.zeros(m, np.uint8)
+        O.b2o_bitunshuffle(ts, m, _libs.ptr(s), _libs.ptr(b), 2)
+        exp[o:o + m] = b
+    assert np.array_equal(g.run_filter(_data.BITSHUFFLE, False, ts, src, bs, version=2), exp)
+
+
+# ---- whole chunks: decode ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("device", [False, True], ids=["host", "device"])
+def test_decode_reference_chunks(device):
+    """Every reference-produced chunk of the golden grid (tests/golden/ref_chunks.npz), in ONE batch."""
+    g = _gpu()
+    chunks = [_golden.ref_chunk(k) for k in _golden.REF_KEYS]
+    res = g.decompress_batch(chunks, device=device)
+    for k, (st, out) in zip(_golden.REF_KEYS, res):
+        assert st == 0, (k, st)
+        assert np.array_equal(out, _data.make_case(_golden.MANIFEST["ref_chunks"][k]["case"])), k
+
+
+@pytest.mark.parametrize("key", _golden.REF_KEYS[::5])
+def test_decode_reference_chunk_single(key):
+    g = _gpu()
+    (st, out), = g.decompress_batch([_golden.ref_chunk(key)])
+    assert st == 0
+    assert np.array_equal(out, _data.make_case(_golden.MANIFEST["ref_chunks"][key]["case"]))
+
+
+@pytest.mark.parametrize("name", _golden.COMPAT_NAMES)
+def test_decode_compat_golden(name):
+    """c-blosc2's own known-answer chunks (compat/*.cdata): Blosc1 16-byte headers, 256 KiB - 2 MiB blocks."""
+    g = _gpu()
+    meta = _golden.MANIFEST["compat"][name]
+    (st, out), = g.decompress_batch([_golden.compat_chunk(name)])
+    assert st == 0, st
+    assert out.size == meta["nbytes"]
+    assert hashlib.sha256(out.tobytes()).hexdigest() == meta["sha256"]
+    exp = _golden.compat_expected(name)
+    if exp is not None:
+        assert np.array_equal(out, exp)
+
+
+def test_decode_malformed_chunks():
+    g = _gpu()
+    for codec in (_data.LZ4, _data.BLOSCLZ, _data.ZSTD):
+        key = [k for k in _golden.REF_KEYS if k.startswith("text_n300000") and "_c%d_" % codec in k][0]
+        chunk = _golden.ref_chunk(key)
+        nbytes = 300000
+        bad = []
+        for cut in (8, 20, 40, chunk.size // 2, chunk.size - 1):
+            bad.append(chunk[:cut].copy())
+        b = chunk.copy(); b[0] = 9; bad.append(b)
+        b = chunk.copy(); b[3] = 0; bad.append(b)
+        b = chunk.copy(); b[32:36] = 0xFF; bad.append(b)
+        b = chunk.copy(); b[chunk.size // 2:chunk.size // 2 + 64] ^= 0x5A; bad.append(b)
+        for device in (False, True):
+            res = g.decompress_batch(bad, caps=[nbytes] * len(bad), device=device)
+            for i, (st, out) in enumerate(res):
+                rc_ref, exp = _libs.oracle_decompress(bad[i], cap=nbytes)
+                if rc_ref < 0:
+                    assert st < 0, (codec, i, st, rc_ref)
+                else:
+                    assert st == 0 and np.array_equal(out, exp)
+        (st, _), = g.decompress_batch([chunk], caps=[nbytes - 1])
+        assert st == -6
+
+
+def test_decode_special_chunks():
+    g = _gpu()
+
+    def hdr(nbytes, ts, special, cbytes=32, blocksize=None):
+        h = np.zeros(32, np.uint8)
+        h[0], h[1], h[2], h[3] = 5, 1, 0x05, ts
+        h[4:8] = np.frombuffer(int(nbytes).to_bytes(4, "little"), np.uint8)
+        h[8:12] = np.frombuffer(int(blocksize or min(nbytes, 32768)).to_bytes(4, "little"), np.uint8)
+        h[12:16] = np.frombuffer(int(cbytes).to_bytes(4, "little"), np.uint8)
+        h[31] = special << 4
+        return h
+    n = 100000
+    chunks = [hdr(n, 4, 1), hdr(n, 4, 2), hdr(n, 8, 2),
+              np.concatenate([hdr(n, 4, 3, cbytes=36), np.array([1, 2, 3, 4], np.uint8)])]
+    for ch, (st, out) in zip(chunks, g.decompress_batch(chunks)):
+        rc, exp = _libs.oracle_decompress(ch)
+        assert rc == n and st == 0
+        assert np.array_equal(out, exp)
+
+
+# ---- whole chunks: compress -----------------------------------------------------------------------------------------
+def _compress_cases():
+    seen, out = set(), []
+    for c in _data.REF_CHUNK_GRID:
+        if c["codec"] in (_data.LZ4, _data.BLOSCLZ) and _data.case_key(c) not in seen:
+            seen.add(_data.case_key(c))
+            out.append(c)
+    return out
+
+
+@pytest.mark.parametrize("case", _compress_cases(), ids=_data.case_key)
+def test_compress_chunks_decodable_by_checker(case):
+    g = _gpu()
+    src = _data.make_case(case)
+    (st, chunk), = g.compress_batch([src], case["codec"], case["clevel"], case["typesize"], case["filter"],
+                                    case["blocksize"])
+    assert st == 0 and chunk.size > 0
+    assert chunk.size <= src.size + 32
+    nb, cb, bs = (int.from_bytes(chunk[o:o + 4].tobytes(), "little") for o in (4, 8, 12))
+    assert nb == src.size and bs == chunk.size
+    rc, back = _checker_decompress(chunk)          # the reference decodes every GPU-produced chunk
+    assert rc == src.size, rc
+    assert np.array_equal(back, src)
+    rc2, back2 = _libs.oracle_decompress(chunk)
+    assert rc2 == src.size and np.array_equal(back2, src)
+    ref_chunk = _golden.ref_chunk(_data.case_key(case))
+    assert chunk[0] == ref_chunk[0] and chunk[3] == ref_chunk[3]
+    assert np.array_equal(chunk[4:12], ref_chunk[4:12])
+    assert np.array_equal(chunk[16:24], ref_chunk[16:24])
+    (st3, back3), = g.decompress_batch([chunk])
+    assert st3 == 0 and np.array_equal(back3, src)
+    # the device-resident entry points give byte-identical chunks for a single-chunk batch of <= 1 block ... and
+    # always decodable ones
+    (st4, chunk4), = g.compress_batch([src], case["codec"], case["clevel"], case["typesize"], case["filter"],
+                                      case["blocksize"], device=True)
+    assert st4 == 0
+    assert np.array_equal(_checker_decompress(chunk4)[1], src)
+
+
+def test_compress_ratio_next_to_reference():
+    """Match choices may differ from the CPU encoder; the ratio must stay in the same league (reported, and bounded
+    loosely here: within 15 % + 64 B of the reference's chunk for the same parameters)."""
+    g = _gpu()
+    for case in _compress_cases():
+        if case["nbytes"] < 50000 or case["kind"] in ("random",):
+            continue
+        src = _data.make_case(case)
+        (st, chunk), = g.compress_batch([src], case["codec"], case["clevel"], case["typesize"], case["filter"],
+                                        case["blocksize"])
+        ref = _golden.MANIFEST["ref_chunks"][_data.case_key(case)]["cbytes"]
+        assert st == 0 and chunk.size <= ref * 1.15 + 64, (_data.case_key(case), chunk.size, ref)
+
+
+def test_compress_batch_lookback_many_ctas():
+    g = _gpu()
+    kinds = ("half", "sensor", "zeros", "random", "text") * 8
+    srcs = [_data.make_data(k, 2000000 + 1000 * i, 2, seed=i) for i, k in enumerate(kinds)]
+    res = g.compress_batch(srcs, _data.LZ4, 9, 2, _data.SHUFFLE, 32768)
+    for s, (st, chunk) in zip(srcs, res):
+        assert st == 0
+        rc, back = _checker_decompress(chunk)
+        assert rc == s.size and np.array_equal(back, s)
+    assert res[2][1].size == 32 and res[2][1][31] == 0x10
+    assert res[3][1].size == srcs[3].size + 32 and (res[3][1][2] & 2)
+    back = g.decompress_batch([c for _, c in res], device=True)
+    for s, (st, out) in zip(srcs, back):
+        assert st == 0 and np.array_equal(out, s)
+
+
+def test_compress_capacity_rules():
+    g = _gpu()
+    src = _data.make_data("random", 50000, 1)
+    (st, chunk), = g.compress_batch([src], _data.LZ4, 5, 1, _data.SHUFFLE, 32768, caps=[50000 + 31], device=True)
+    assert st == 0 and chunk.size == 0
+    src = _data.make_data("text", 50000, 1)
+    (st, chunk), = g.compress_batch([src], _data.LZ4, 5, 1, _data.SHUFFLE, 32768, caps=[40000], device=True)
+    assert st == 0 and 0 < chunk.size <= 40000
+    assert np.array_equal(_checker_decompress(chunk)[1], src)
+    (st, chunk), = g.compress_batch([np.zeros(0, np.uint8)], _data.LZ4, 5, 1, _data.SHUFFLE, 32768)
+    assert st == 0 and chunk.size == 32
+    assert _checker_decompress(chunk)[0] == 0
+
+
+def test_unsupported_encoders_fail_loudly():
+    """zstd / lz4hc ENCODE is out of scope: the call fails, it does not fall back to a CPU."""
+    from compressed_image_b200 import _b2g
+    g = _gpu()
+    src = _data.make_data("text", 50000, 1)
+    for codec in (_data.ZSTD, _data.LZ4HC):
+        with pytest.raises(_b2g.B2GError) as e:
+            g.compress_batch([src], codec, 5, 1, _data.SHUFFLE, 32768)
+        assert e.value.code == -7
