@@ -278,7 +278,9 @@ def run_b2g(args, rank, world, local_rank):
         ctx.compress_batch(hcomp, stream=sh)
 
     e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(3):
+    if args.kernels_only:
+        e2e_steps = 1
+    for _ in range(1 if args.kernels_only else 3):
         e2e_step()
     assert all(hdec[k].status == 0 for k in range(n)) and all(hcomp[k].status == 0 for k in range(n))
     assert torch.equal(h_out, h_raw), "e2e round trip mismatch"
@@ -326,7 +328,7 @@ def run_b2g(args, rank, world, local_rank):
     cpu = None
     L = ref_lib()
     cores = os.cpu_count() or 1
-    if L is not None:
+    if L is not None and not args.kernels_only:
         sample = list(range(n)) if cores >= 16 else list(range(0, n, 4))
         dt, ref_chunks = cpu_reference_pass(L, pieces, [order[i] for i in sample], cores, repeat=2)
         sb = sum(int(pieces[order[i]].size) for i in sample)
@@ -356,6 +358,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b2g", choices=["b2g", "reference"])
+    ap.add_argument("--kernels-only", action="store_true", help="profiling runs: skip the e2e and cpu_baseline legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

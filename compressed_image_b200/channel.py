@@ -263,9 +263,12 @@ class Channel:
         for i in range(len(self._chunks)):
             buf = self.get_chunk(i)
             before = buf.copy()
-            yield buf
-            if not np.array_equal(before.view(np.uint8), buf.view(np.uint8)):
-                self.set_chunk(i, buf)
+            try:
+                yield buf
+            finally:   # also runs when the iteration is abandoned (zip over channels stops at the first exhausted
+                # iterator): the reference flushes the last chunk in ~channel_iterator (iterator.h:72-93)
+                if not np.array_equal(before.view(np.uint8), buf.view(np.uint8)):
+                    self.set_chunk(i, buf)
 
     def chunks(self):
         """The stored chunk bytes (numpy uint8 arrays; lazy chunks are materialised as blosc2 special chunks)."""

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -96,6 +97,18 @@ struct b2g_ctx {
 
 namespace {
 
+std::mutex g_attr_mutex;
+size_t g_smem_limit[64][4];  // [device][kernel]
+
+int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
+  std::lock_guard<std::mutex> lock(g_attr_mutex);
+  size_t& cur = g_smem_limit[dev & 63][which];
+  if (bytes <= cur) return 0;
+  CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  cur = bytes;
+  return 0;
+}
+
 int set_geometry(b2g_ctx* c, int blocksize) {
   // (re)derive shared-memory sizes, grids and the slab for a given maximum blocksize
   if (c->geometry_ready && blocksize <= c->blocksize) return 0;
@@ -105,12 +118,14 @@ int set_geometry(b2g_ctx* c, int blocksize) {
   c->dec_smem = (size_t)c->win_bytes + kDecodeSharedBytes;
   c->decz_smem = (size_t)c->win_bytes + kDecodeSharedBytes + sizeof(ZWork) * kCtaWarps;
   c->comp_smem = (size_t)c->win_bytes + (size_t)plan_htab_bytes(c->win_bytes) + kCompressSharedBytes;
-  CU(cudaFuncSetAttribute(k_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->dec_smem));
-  CU(cudaFuncSetAttribute(k_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->decz_smem));
+  // The dynamic shared-memory limit is a per-function (per-device) attribute shared by every context of the process:
+  // only ever raise it, or a context sized for small blocks would cut off one sized for large blocks.
+  if (int rc = raise_smem_limit(c->dev, 0, (const void*)k_decode<false>, c->dec_smem)) return rc;
+  if (int rc = raise_smem_limit(c->dev, 1, (const void*)k_decode<true>, c->decz_smem)) return rc;
   if (c->comp_smem <= 227 * 1024)
-    CU(cudaFuncSetAttribute(k_compress, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->comp_smem));
+    if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, c->comp_smem)) return rc;
   if (c->win_bytes <= 227 * 1024)
-    CU(cudaFuncSetAttribute(k_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, c->win_bytes));
+    if (int rc = raise_smem_limit(c->dev, 3, (const void*)k_filter, (size_t)c->win_bytes)) return rc;
   int occ = 0;
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, kCtaThreads, c->dec_smem));
   c->dec_grid = c->sms * std::max(occ, 1);
