@@ -82,9 +82,12 @@ struct b2g_ctx {
   int64_t launches = 0;
   // geometry
   int blocksize = 32768;   // context blocksize (compress) / largest block the device decode path is sized for
-  int win_bytes = 32768;   // shared-memory window
+  int win_bytes = 32768;   // shared-memory window (decode, filters)
+  int cwin_bytes = 32768;  // shared-memory window (compress)
   size_t dec_smem = 0, decz_smem = 0, comp_smem = 0;
   int dec_grid = 0, decz_grid = 0, comp_grid = 0;
+  int dec_threads = kCtaThreads, comp_threads = kCtaThreads;  // 32 x streams per block (<= kCtaWarps warps)
+  int htab_bytes = 4096;                                      // per-warp encoder hash table
   bool geometry_ready = false;
   // device + pinned work buffers
   DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_desc, d_slab, d_in, d_out;
@@ -109,41 +112,59 @@ int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
   return 0;
 }
 
+size_t slab_stride(const b2g_ctx* c);
+
+// Compress geometry: fixed at creation from the context's own parameters.
+int set_compress_geometry(b2g_ctx* c) {
+  const int bs = std::max(c->p.blocksize, 1);
+  c->cwin_bytes = std::max((int)align_up((size_t)bs, 16), 1024);
+  // CTA width: one warp per stream of a block
+  const int cstreams = plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, bs);
+  const int cwarps = plan_cta_warps(cstreams);
+  c->comp_threads = 32 * cwarps;
+  c->htab_bytes = plan_htab_bytes(bs / cstreams);
+  c->comp_smem = (size_t)c->cwin_bytes + (size_t)cwarps * (size_t)(c->htab_bytes + kEncWorkBytes) + kCompressSharedBytes;
+  c->comp_grid = 0;
+  if (c->comp_smem > 227 * 1024) return 0;  // compress calls on this context report B2G_ERR_BLOCKSIZE
+  if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, c->comp_smem)) return rc;
+  int occ = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, c->comp_threads, c->comp_smem));
+  c->comp_grid = c->sms * std::max(occ, 1);
+  return 0;
+}
+
+// Decode geometry: (re)derived for the largest blocksize seen so far (host-pointer calls read it from the headers).
 int set_geometry(b2g_ctx* c, int blocksize) {
-  // (re)derive shared-memory sizes, grids and the slab for a given maximum blocksize
   if (c->geometry_ready && blocksize <= c->blocksize) return 0;
   c->blocksize = std::max(blocksize, 1);
   const int win = (int)align_up((size_t)std::min(c->blocksize, kMaxSmemWindow), 16);
   c->win_bytes = std::max(win, 1024);
   c->dec_smem = (size_t)c->win_bytes + kDecodeSharedBytes;
   c->decz_smem = (size_t)c->win_bytes + kDecodeSharedBytes + sizeof(ZWork) * kCtaWarps;
-  c->comp_smem = (size_t)c->win_bytes + (size_t)plan_htab_bytes(c->win_bytes) + kCompressSharedBytes;
+  // CTA width: one warp per stream; the context's typesize is the hint for the chunks it will see (any chunk still
+  // decodes: a warp then takes several streams in turn)
+  c->dec_threads = 32 * plan_cta_warps(c->p.typesize <= kMaxStreams ? c->p.typesize : 1);
   // The dynamic shared-memory limit is a per-function (per-device) attribute shared by every context of the process:
   // only ever raise it, or a context sized for small blocks would cut off one sized for large blocks.
   if (int rc = raise_smem_limit(c->dev, 0, (const void*)k_decode<false>, c->dec_smem)) return rc;
   if (int rc = raise_smem_limit(c->dev, 1, (const void*)k_decode<true>, c->decz_smem)) return rc;
-  if (c->comp_smem <= 227 * 1024)
-    if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, c->comp_smem)) return rc;
-  if (c->win_bytes <= 227 * 1024)
-    if (int rc = raise_smem_limit(c->dev, 3, (const void*)k_filter, (size_t)c->win_bytes)) return rc;
+  if (int rc = raise_smem_limit(c->dev, 3, (const void*)k_filter, (size_t)c->win_bytes)) return rc;
   int occ = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, kCtaThreads, c->dec_smem));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, c->dec_threads, c->dec_smem));
   c->dec_grid = c->sms * std::max(occ, 1);
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, kCtaThreads, c->decz_smem));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, c->dec_threads, c->decz_smem));
   c->decz_grid = c->sms * std::max(occ, 1);
-  occ = 0;
-  if (c->comp_smem <= 227 * 1024)
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, kCtaThreads, c->comp_smem));
-  c->comp_grid = c->sms * std::max(occ, 1);
   // slab: compressed streams of one block per compress CTA; whole blocks for oversized decode blocks
-  const size_t stride = align_up((size_t)c->blocksize + 16 * kMaxStreams + 256, 256);
+  const size_t stride = slab_stride(c);
   const int grid = std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid));
   if (int rc = c->d_slab.ensure(stride * (size_t)grid)) return rc;
   c->geometry_ready = true;
   return 0;
 }
 
-size_t slab_stride(const b2g_ctx* c) { return align_up((size_t)c->blocksize + 16 * kMaxStreams + 256, 256); }
+size_t slab_stride(const b2g_ctx* c) {
+  return align_up((size_t)std::max(c->blocksize, c->p.blocksize) + 16 * kMaxStreams + 256, 256);
+}
 
 int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd) {
   if (int rc = c->d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
@@ -176,12 +197,12 @@ int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool
   da.win_bytes = c->win_bytes;
   da.slab = (uint8_t*)c->d_slab.p;
   da.slab_stride = (int64_t)slab_stride(c);
-  k_decode<false><<<c->dec_grid, kCtaThreads, c->dec_smem, s>>>(da);
+  k_decode<false><<<c->dec_grid, c->dec_threads, c->dec_smem, s>>>(da);
   c->launches++;
   if (want_zstd) {
     da.base = pa.base + (n + 1);
     da.ctl = pa.ctl + 1;
-    k_decode<true><<<c->decz_grid, kCtaThreads, c->decz_smem, s>>>(da);
+    k_decode<true><<<c->decz_grid, c->dec_threads, c->decz_smem, s>>>(da);
     c->launches++;
   }
   CU(cudaEventRecord(c->ev[2], s));
@@ -204,7 +225,7 @@ int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, in
   CParams cp;
   cp.codec = p.codec; cp.clevel = p.clevel; cp.typesize = p.typesize; cp.filter = p.filter;
   for (int i = 0; i < n; i++) {
-    const int nit = plan_compress_chunk(ci[i], cp, c->p.blocksize, nbytes[i], h_desc[i].dst_cap, c->win_bytes);
+    const int nit = plan_compress_chunk(ci[i], cp, c->p.blocksize, nbytes[i], h_desc[i].dst_cap, c->cwin_bytes);
     ci[i].item_base = (int32_t)items;
     base[i] = (int32_t)items;
     items += nit;
@@ -238,11 +259,11 @@ int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, in
   ca.slab = (uint8_t*)c->d_slab.p;
   ca.slab_stride = (int64_t)slab_stride(c);
   ca.n = n;
-  ca.win_bytes = c->win_bytes;
-  ca.htab_bytes = plan_htab_bytes(c->win_bytes);
+  ca.win_bytes = c->cwin_bytes;
+  ca.htab_bytes = c->htab_bytes;
   ca.p = cp;
   const int cgrid = (int)std::min<int64_t>(c->comp_grid, items);
-  k_compress<<<cgrid, kCtaThreads, c->comp_smem, s>>>(ca);
+  k_compress<<<cgrid, c->comp_threads, c->comp_smem, s>>>(ca);
   c->launches++;
   FinalizeArgs fa;
   fa.chunks = ca.chunks;
@@ -302,6 +323,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
             !cuda_fail(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev), "sm count") &&
             !cuda_fail(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate");
   for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&c->ev[i]), "cudaEventCreate");
+  if (ok) ok = set_compress_geometry(c) == 0;
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;
   if (!ok) { b2g_destroy(c); return nullptr; }
   return c;

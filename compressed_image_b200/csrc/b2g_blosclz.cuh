@@ -78,103 +78,4 @@ __device__ __forceinline__ int blosclz_put_literals(const uint8_t* in, int ancho
   return op + total;
 }
 
-// Compresses in[0..n) (shared memory) into out[0..cap).  Returns the size or 0 (does not fit / too small: the
-// caller stores the stream raw).  Same search structure as lz4_encode_warp, blosclz emission.
-__device__ __forceinline__ int blosclz_encode_warp(const uint8_t* in, int n, uint8_t* out, int cap, uint16_t* htab,
-                                                   int hlog) {
-  const int lane = lane_id();
-  if (n < 16 || cap < 66) return 0;  // blosclz.c:480-482
-  const int iplimit = n - 13;    // last position probed (blosclz.c ip_limit = length - 12, exclusive)
-  const int matchlimit = n - 4;  // matches end at or before this; the rest is the closing literal run
-  int ip = 1, anchor = 0, op = 0;
-  for (int i = lane; i < (1 << hlog); i += 32) htab[i] = 0;
-  __syncwarp();
-  int miss = 0;
-  while (ip <= iplimit) {
-    const int p = ip + lane;
-    const bool live = p <= iplimit;
-    uint32_t seq = 0, h = 0;
-    int cand = -1;
-    if (live) {
-      seq = ld32_any(in + p);
-      h = (seq * 2654435761u) >> (32 - hlog);
-      cand = p - (int)((uint32_t)(p - (int)htab[h]) & 0xffffu);
-    }
-    bool hit = live && cand >= 0 && cand < p && ld32_any(in + cand) == seq;
-    unsigned m = __ballot_sync(kFull, hit);
-    // insert only the positions up to the winning one: later positions are probed again and must still
-    // find their older candidates (every lane has read the table before any lane writes it)
-    if (live && (m == 0 || lane <= __ffs((int)m) - 1)) htab[h] = (uint16_t)p;
-    if (m == 0) {
-      miss++;
-      ip += 32 + ((miss >> 3) << 5);
-      __syncwarp();
-      continue;
-    }
-    miss = 0;
-    const int w = __ffs((int)m) - 1;
-    int mp = ip + w;
-    int mc = __shfl_sync(kFull, cand, w);
-    {
-      int back = 0;
-      const int maxback = min(mp - anchor, mc);
-      while (back < maxback) {
-        int i = back + lane;
-        bool eq = i < maxback && in[mp - 1 - i] == in[mc - 1 - i];
-        unsigned e = __ballot_sync(kFull, !eq);
-        if (e) { back += __ffs((int)e) - 1; break; }
-        back += 32;
-      }
-      if (back > maxback) back = maxback;
-      mp -= back;
-      mc -= back;
-    }
-    const int ml = 4 + warp_match_len(in + mp + 4, in + mc + 4, matchlimit - (mp + 4), lane);
-    const int db = mp - mc - 1;  // biased distance
-    const bool far = db >= kBlzMaxDistance;
-    if (far && ml < 8) {  // a 4-byte far token does not pay for a short match: treat the position as a literal
-      ip = ip + w + 1;
-      __syncwarp();
-      continue;
-    }
-    const int lit = mp - anchor;
-    const int L = ml - 2;
-    {
-      int need = lit + ((lit + 31) >> 5) + 1 + (L >= 7 ? (L - 7) / 255 + 1 : 0) + (far ? 3 : 1);
-      if (op + need + (n - (mp + ml)) / 32 + 6 > cap) return 0;
-    }
-    if (lit > 0) op = blosclz_put_literals(in, anchor, lit, out, op, lane);
-    const int dd = far ? db - kBlzMaxDistance : db;
-    const int hi5 = far ? 31 : (db >> 8);
-    if (lane == 0) out[op] = (uint8_t)(((L >= 7 ? 7 : L) << 5) | hi5);
-    op++;
-    if (L >= 7) op = lz4_put_varlen(out, op, L - 7, lane);
-    if (lane == 0) {
-      if (far) {
-        out[op] = 255;
-        out[op + 1] = (uint8_t)(dd >> 8);
-        out[op + 2] = (uint8_t)dd;
-      } else {
-        out[op] = (uint8_t)db;
-      }
-    }
-    op += far ? 3 : 1;
-    ip = mp + ml;
-    anchor = ip;
-    if (lane < 2 && ip - 2 + lane <= iplimit && ip - 2 + lane > 0) {
-      int q = ip - 2 + lane;
-      uint32_t s2 = ld32_any(in + q);
-      htab[(s2 * 2654435761u) >> (32 - hlog)] = (uint16_t)q;
-    }
-    __syncwarp();
-  }
-  const int lit = n - anchor;  // >= 4: the closing literal run
-  if (op + lit + ((lit + 31) >> 5) > cap) return 0;
-  op = blosclz_put_literals(in, anchor, lit, out, op, lane);
-  __syncwarp();
-  if (lane == 0) out[0] |= 32;  // codec marker (blosclz.c:613)
-  __syncwarp();
-  return op;
-}
-
 }  // namespace b2g

@@ -13,7 +13,7 @@
 //   k_finalize      chunk headers, SPECIAL_ZERO and memcpyed fallbacks (blosc2.c:2393-2529).
 //   k_filter        standalone filters (K1-K4).
 #pragma once
-#include "b2g_blosclz.cuh"
+#include "b2g_lzenc.cuh"
 #include "b2g_filters.cuh"
 #include "b2g_zstd.cuh"
 
@@ -221,6 +221,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
   DecodeShared* sh = (DecodeShared*)(smem + a.win_bytes);      // win_bytes is a multiple of 16
   ZWork* zwork = (ZWork*)(smem + a.win_bytes + 256);           // [kCtaWarps] when Z
   const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
+  const int nthr = (int)blockDim.x, nwarps = nthr >> 5;  // 32 x (streams per block, at most kCtaWarps)
   int hint = 0;
   for (;;) {
     __syncthreads();  // previous item fully retired (window + sh reusable)
@@ -246,21 +247,21 @@ __global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
 
     if (d.special) {  // blosc2.c:1694-1718
       if (d.special == 1 || d.special == 4) {
-        fill_bytes(raw, 0, bsize, tid, kCtaThreads);  // 4 = uninitialised: any content is legal, zeros are stable
+        fill_bytes(raw, 0, bsize, tid, nthr);  // 4 = uninitialised: any content is legal, zeros are stable
       } else if (d.special == 2) {
         if (d.typesize == 4) {
-          for (int i = tid; i < bsize / 4; i += kCtaThreads) st_le32(raw + 4 * i, 0x7fc00000);
+          for (int i = tid; i < bsize / 4; i += nthr) st_le32(raw + 4 * i, 0x7fc00000);
         } else {
-          for (int i = tid; i < bsize / 8; i += kCtaThreads) { st_le32(raw + 8 * i, 0); st_le32(raw + 8 * i + 4, 0x7ff80000); }
+          for (int i = tid; i < bsize / 8; i += nthr) { st_le32(raw + 8 * i, 0); st_le32(raw + 8 * i + 4, 0x7ff80000); }
         }
       } else {
         const size_t o = (size_t)j * d.blocksize;
-        for (int i = tid; i < bsize; i += kCtaThreads) raw[i] = ch.src[kHdrExt + (o + i) % d.vts];
+        for (int i = tid; i < bsize; i += nthr) raw[i] = ch.src[kHdrExt + (o + i) % d.vts];
       }
       continue;
     }
     if (d.memcpyed) {
-      copy_bytes(raw, ch.src + d.hdr + (size_t)j * d.blocksize, bsize, tid, kCtaThreads);
+      copy_bytes(raw, ch.src + d.hdr + (size_t)j * d.blocksize, bsize, tid, nthr);
       continue;
     }
 
@@ -299,7 +300,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
     const bool direct = d.filter == kFilterNone;
     uint8_t* win = direct ? raw
                           : (bsize <= a.win_bytes ? win_s : a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride);
-    for (int s = warp; s < nstreams; s += kCtaWarps) {
+    for (int s = warp; s < nstreams; s += nwarps) {
       const int32_t pos = sh->spos[s];
       int rc = decode_stream<Z>(d.fmt, ch.src + pos, sh->scsize[s], srcsize - pos, win + (size_t)s * neblock,
                                 neblock, Z ? zwork + warp : nullptr);
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
       if (tid == 0) set_status(a.res, c, sh->err);
       continue;
     }
-    if (!direct) filter_backward(d.filter, d.typesize, bsize, win, raw, d.version, tid, kCtaThreads);
+    if (!direct) filter_backward(d.filter, d.typesize, bsize, win, raw, d.version, tid, nthr);
   }
 }
 
@@ -326,8 +327,8 @@ struct CompressArgs {
   int64_t slab_stride;
   int32_t n;
   int32_t win_bytes;
-  int32_t htab_bytes;            // shared hash-table region: each active warp gets (1 << hlog) uint16 entries, hlog
-                                 // chosen per block so that a stream of neblock bytes owns neblock / 2 table bytes
+  int32_t htab_bytes;            // per-warp hash table bytes (a power of two); each warp's work area is
+                                 // htab_bytes + kEncWorkBytes, see enc_work()
   CParams p;
 };
 
@@ -361,11 +362,14 @@ __device__ __forceinline__ bool warp_is_run(const uint8_t* in, int n, int lane) 
 }
 
 __global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
+  // blockDim.x = 32 x (streams per block, at most kCtaWarps): every warp of the CTA owns a stream
   uint8_t* smem = dyn_smem();
   uint8_t* win = smem;                                            // [win_bytes] filtered block
-  uint16_t* htabs = (uint16_t*)(smem + a.win_bytes);              // [kCtaWarps][1 << hlog]
-  CompressShared* sh = (CompressShared*)(smem + a.win_bytes + a.htab_bytes);
   const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
+  const int nthr = (int)blockDim.x, nwarps = nthr >> 5;
+  const int work_bytes = a.htab_bytes + kEncWorkBytes;
+  uint8_t* work = smem + a.win_bytes + (size_t)warp * work_bytes;
+  CompressShared* sh = (CompressShared*)(smem + a.win_bytes + (size_t)nwarps * work_bytes);
   uint8_t* slab = a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride;
   int hint = 0;
   for (;;) {
@@ -389,15 +393,16 @@ __global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
     const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
     const int32_t bsize = is_left ? d.leftover : d.blocksize;
     const int ts = a.p.typesize;
-    filter_forward(a.p.filter, ts, bsize, ch.src + (size_t)j * d.blocksize, win, tid, kCtaThreads);
+    filter_forward(a.p.filter, ts, bsize, ch.src + (size_t)j * d.blocksize, win, tid, nthr);
     __syncthreads();
     const int nstreams = (!d.dont_split && !is_left) ? ts : 1;
     const int32_t neblock = bsize / nstreams;
     const int32_t sstride = (neblock + 15) & ~15;  // slab region per stream
-    int hlog = 29 - __clz(neblock);                // floor(log2(neblock)) - 2: table bytes <= neblock / 2
-    hlog = hlog < 6 ? 6 : (hlog > 13 ? 13 : hlog);
-    uint16_t* htab = htabs + ((size_t)warp << hlog);
-    for (int s = warp; s < nstreams; s += kCtaWarps) {
+    int hlog = 28 - __clz(neblock);                // floor(log2(neblock)) - 3: table bytes <= neblock / 4
+    const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
+    hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
+    const EncWork ew = enc_work(work, a.htab_bytes, hlog);
+    for (int s = warp; s < nstreams; s += nwarps) {
       const uint8_t* in = win + (size_t)s * neblock;
       uint8_t* out = slab + (size_t)s * sstride;
       int32_t psize, csize, raw = 0;
@@ -409,8 +414,8 @@ __global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
       } else {
         int r = 0;
         const int cap = neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
-        if (a.p.codec == kCodecLz4) r = lz4_encode_warp(in, neblock, out, cap, htab, hlog);
-        else r = blosclz_encode_warp(in, neblock, out, cap, htab, hlog);
+        if (a.p.codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(in, neblock, out, cap, ew);
+        else r = lz_encode_warp<kCodecBlosclz>(in, neblock, out, cap, ew);
         if (r <= 0 || r >= neblock) { raw = 1; psize = csize = neblock; }
         else psize = csize = r;
       }
@@ -469,7 +474,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
       uint8_t* o = ch.dst + off;
       if (tid == 0) st_le32(o, sh->csize[s]);
       const uint8_t* from = sh->raw[s] ? win + (size_t)s * neblock : slab + (size_t)s * sstride;
-      copy_bytes(o + 4, from, ps, tid, kCtaThreads);
+      copy_bytes(o + 4, from, ps, tid, nthr);
       off += 4 + ps;
     }
   }

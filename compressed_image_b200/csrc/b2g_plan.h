@@ -44,8 +44,19 @@ inline int plan_compress_chunk(CInfo& d, const CParams& p, int user_blocksize, i
   return std::max(d.nblocks, 1);
 }
 
-// Shared hash-table region of the encoder for a given window: half the window (see k_compress), at least 4 x 64
-// entries, at most 4 x 8192 entries.
-inline int plan_htab_bytes(int win_bytes) { return std::min(std::max(win_bytes / 2, 1024), 4 * 16384); }
+// Streams a block of this geometry is stored as (stune.c:185-210), and the warps a CTA gets for it.
+inline int plan_nstreams(int codec, int clevel, int filter, int typesize, int blocksize) {
+  return plan_split_block(codec, clevel, filter, typesize, blocksize) ? typesize : 1;
+}
+inline int plan_cta_warps(int nstreams) { return std::min(std::max(nstreams, 1), kCtaWarps); }
+
+// Per-warp hash table of the encoder for streams of `neblock` bytes: 2^hlog uint16 entries with
+// hlog = floor(log2(neblock)) - 3 clamped to [6, 12] (table bytes <= neblock / 4; k_compress derives the same hlog).
+inline int plan_htab_bytes(int neblock) {
+  int lg = 0;
+  while ((2 << lg) <= std::max(neblock, 1)) lg++;   // floor(log2(neblock))
+  const int hlog = std::min(std::max(lg - 3, 6), 12);
+  return 2 << hlog;
+}
 
 }  // namespace b2g

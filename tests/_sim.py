@@ -59,7 +59,7 @@ def decompress_batch(chunks, caps=None, win_bytes=32768, max_block=None, grid=2,
     return res
 
 
-def compress_batch(srcs, codec, clevel, typesize, filt, blocksize, caps=None, win_bytes=32768, grid=2, hlog=12):
+def compress_batch(srcs, codec, clevel, typesize, filt, blocksize, caps=None, win_bytes=32768, grid=2, hlog=0):
     """-> list of (status, chunk bytes)."""
     n = len(srcs)
     srcs = [np.ascontiguousarray(s).view(np.uint8).reshape(-1) for s in srcs]

@@ -59,7 +59,7 @@ cusim_switch:
 
 namespace cusim {
 
-enum Op : uint8_t { OP_NONE, OP_SYNCWARP, OP_SHFL, OP_BALLOT, OP_ANY, OP_ALL, OP_REDUCE };
+enum Op : uint8_t { OP_NONE, OP_SYNCWARP, OP_SHFL, OP_BALLOT, OP_ANY, OP_ALL, OP_REDUCE, OP_MATCH };
 
 struct Warp {
   uint64_t slot[2][32];
@@ -305,6 +305,15 @@ static inline unsigned __ballot_sync(unsigned, int pred) {
   cusim::Warp* w = cusim::S().cur->warp;
   for (int i = 0; i < 32; i++)
     if (w->slot[p][i] & 1) r |= 1u << i;
+  return r;
+}
+// __match_any_sync(full mask, v): the lanes holding the same value
+static inline unsigned cusim_match_any(unsigned v) {
+  int p = cusim::warp_rendezvous(v, cusim::OP_MATCH);
+  unsigned r = 0;
+  cusim::Warp* w = cusim::S().cur->warp;
+  for (int i = 0; i < 32; i++)
+    if ((unsigned)w->slot[p][i] == v) r |= 1u << i;
   return r;
 }
 static inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }

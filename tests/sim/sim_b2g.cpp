@@ -86,10 +86,13 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   CompressArgs ca;
   ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
   ca.desc = desc.data(); ca.slab = slab.data(); ca.slab_stride = (int64_t)stride; ca.n = n;
-  ca.win_bytes = win_bytes; ca.htab_bytes = plan_htab_bytes(win_bytes); ca.p = p;
-  const size_t smem = (size_t)win_bytes + (size_t)plan_htab_bytes(win_bytes) + 256;
-  (void)hlog;
-  cusim::launch(dim3(grid), dim3(kCtaThreads), smem, [&] { k_compress(ca); });
+  const int bs = plan_blocksize(blocksize, typesize, 1 << 30);
+  const int nstreams = plan_nstreams(codec, clevel, filter, typesize, bs);
+  const int nwarps = plan_cta_warps(nstreams);
+  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(bs / nstreams);
+  ca.win_bytes = win_bytes; ca.htab_bytes = htab_bytes; ca.p = p;
+  const size_t smem = (size_t)win_bytes + (size_t)nwarps * (htab_bytes + kEncWorkBytes) + 256;
+  cusim::launch(dim3(grid), dim3(32 * nwarps), smem, [&] { k_compress(ca); });
   FinalizeArgs fa;
   fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.res = res.data(); fa.base = base.data();
   fa.n = n; fa.total_items = (int32_t)items; fa.p = p;
@@ -128,14 +131,14 @@ int sim_stream_decode(int fmt, const void* src, int n, void* dst, int cap) {
 int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int hlog) {
   int result = 0;
   const size_t in_bytes = au((size_t)n + 16, 16);
-  cusim::launch(dim3(1), dim3(32), in_bytes + (2u << hlog), [&] {
+  cusim::launch(dim3(1), dim3(32), in_bytes + (2u << hlog) + kEncWorkBytes, [&] {
     uint8_t* in = dyn_smem();
     for (int i = (int)threadIdx.x; i < n; i += 32) in[i] = ((const uint8_t*)src)[i];
     __syncwarp();
-    uint16_t* ht = (uint16_t*)(in + in_bytes);
+    const EncWork ew = enc_work(in + in_bytes, 2 << hlog, hlog);
     int r;
-    if (codec == kCodecLz4) r = lz4_encode_warp(in, n, (uint8_t*)dst, cap, ht, hlog);
-    else r = blosclz_encode_warp(in, n, (uint8_t*)dst, cap, ht, hlog);
+    if (codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(in, n, (uint8_t*)dst, cap, ew);
+    else r = lz_encode_warp<kCodecBlosclz>(in, n, (uint8_t*)dst, cap, ew);
     if (threadIdx.x == 0) result = r;
   });
   return result;
