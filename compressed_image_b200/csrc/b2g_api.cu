@@ -73,11 +73,29 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace
 
+// One pipeline lane: a stream plus every per-batch work buffer, so that sub-batches of a host-pointer call can be in
+// flight on different lanes at once (H2D of one overlapping the kernels of another and the D2H of a third).  The
+// device-resident entry points use lane 0 on the caller's stream.
+constexpr int kLanes = 3;
+struct Lane {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
+  cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_desc, d_slab;
+  HostBuf h_chunks, h_res, h_cinfo, h_base;
+  void release() {
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_desc, &d_slab}) b->release();
+    for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
+    for (auto& e : ev) if (e) cudaEventDestroy(e);
+    if (res_ready) cudaEventDestroy(res_ready);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
 struct b2g_ctx {
   b2g_params p{};
   int dev = 0, sms = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  Lane lanes[kLanes];
   float last_ms[2] = {0, 0};
   int64_t launches = 0;
   // geometry
@@ -90,8 +108,7 @@ struct b2g_ctx {
   int htab_bytes = 4096;                                      // per-warp encoder hash table
   bool geometry_ready = false;
   // device + pinned work buffers
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_desc, d_slab, d_in, d_out;
-  HostBuf h_chunks, h_res, h_cinfo, h_base;
+  DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
   // in-flight batch (device-resident API)
   b2g_chunk* pend = nullptr;
   int pend_n = 0;
@@ -154,10 +171,6 @@ int set_geometry(b2g_ctx* c, int blocksize) {
   c->dec_grid = c->sms * std::max(occ, 1);
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, c->dec_threads, c->decz_smem));
   c->decz_grid = c->sms * std::max(occ, 1);
-  // slab: compressed streams of one block per compress CTA; whole blocks for oversized decode blocks
-  const size_t stride = slab_stride(c);
-  const int grid = std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid));
-  if (int rc = c->d_slab.ensure(stride * (size_t)grid)) return rc;
   c->geometry_ready = true;
   return 0;
 }
@@ -166,27 +179,29 @@ size_t slab_stride(const b2g_ctx* c) {
   return align_up((size_t)std::max(c->blocksize, c->p.blocksize) + 16 * kMaxStreams + 256, 256);
 }
 
-int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd) {
-  if (int rc = c->d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
-  if (int rc = c->d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
-  if (int rc = c->d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
-  if (int rc = c->d_base.ensure(sizeof(int32_t) * 2 * ((size_t)n + 1))) return rc;
-  if (int rc = c->d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
-  if (int rc = c->h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
-  CU(cudaMemcpyAsync(c->d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
-  CU(cudaEventRecord(c->ev[0], s));
+int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd) {
+  // slab: whole blocks for decode blocks larger than the shared window, one per CTA
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid)))) return rc;
+  if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  if (int rc = L.d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
+  if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (int rc = L.d_base.ensure(sizeof(int32_t) * 2 * ((size_t)n + 1))) return rc;
+  if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
+  if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(L.ev[0], s));
   PlanArgs pa;
-  pa.chunks = (const DChunk*)c->d_chunks.p;
-  pa.info = (DInfo*)c->d_info.p;
-  pa.res = (DResult*)c->d_res.p;
-  pa.base = (int32_t*)c->d_base.p;
-  pa.ctl = (BatchCtl*)c->d_ctl.p;
+  pa.chunks = (const DChunk*)L.d_chunks.p;
+  pa.info = (DInfo*)L.d_info.p;
+  pa.res = (DResult*)L.d_res.p;
+  pa.base = (int32_t*)L.d_base.p;
+  pa.ctl = (BatchCtl*)L.d_ctl.p;
   pa.n = n;
   pa.max_block = c->blocksize;
   pa.zstd_ok = want_zstd ? 1 : 0;
   k_plan_decode<<<1, 1024, 2 * 1024 * sizeof(int32_t), s>>>(pa);
   c->launches++;
-  CU(cudaEventRecord(c->ev[1], s));
+  CU(cudaEventRecord(L.ev[1], s));
   DecodeArgs da;
   da.chunks = pa.chunks;
   da.info = pa.info;
@@ -195,7 +210,7 @@ int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool
   da.ctl = pa.ctl;
   da.n = n;
   da.win_bytes = c->win_bytes;
-  da.slab = (uint8_t*)c->d_slab.p;
+  da.slab = (uint8_t*)L.d_slab.p;
   da.slab_stride = (int64_t)slab_stride(c);
   k_decode<false><<<c->dec_grid, c->dec_threads, c->dec_smem, s>>>(da);
   c->launches++;
@@ -205,22 +220,24 @@ int enqueue_decode(b2g_ctx* c, const DChunk* h_desc, int n, cudaStream_t s, bool
     k_decode<true><<<c->decz_grid, c->dec_threads, c->decz_smem, s>>>(da);
     c->launches++;
   }
-  CU(cudaEventRecord(c->ev[2], s));
+  CU(cudaEventRecord(L.ev[2], s));
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(c->h_res.p, c->d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(L.h_res.p, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaEventRecord(L.res_ready, s));
   return 0;
 }
 
-int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
+int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid)))) return rc;
   const b2g_params& p = c->p;
   if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
   if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
   if (p.clevel > 9) return B2G_ERR_CODEC_PARAM;
   if (c->comp_smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
-  if (int rc = c->h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
-  if (int rc = c->h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
-  CInfo* ci = (CInfo*)c->h_cinfo.p;
-  int32_t* base = (int32_t*)c->h_base.p;
+  if (int rc = L.h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+  if (int rc = L.h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
+  CInfo* ci = (CInfo*)L.h_cinfo.p;
+  int32_t* base = (int32_t*)L.h_base.p;
   int64_t items = 0;
   CParams cp;
   cp.codec = p.codec; cp.clevel = p.clevel; cp.typesize = p.typesize; cp.filter = p.filter;
@@ -232,31 +249,31 @@ int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, in
     if (items > INT32_MAX) return B2G_ERR_MAX_BUFSIZE;
   }
   base[n] = (int32_t)items;
-  if (int rc = c->d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
-  if (int rc = c->d_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
-  if (int rc = c->d_state.ensure(sizeof(CState) * (size_t)n)) return rc;
-  if (int rc = c->d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
-  if (int rc = c->d_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
-  if (int rc = c->d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
-  if (int rc = c->d_desc.ensure(sizeof(unsigned long long) * (size_t)items)) return rc;
-  if (int rc = c->h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
-  CU(cudaMemcpyAsync(c->d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
-  CU(cudaMemcpyAsync(c->d_cinfo.p, ci, sizeof(CInfo) * (size_t)n, cudaMemcpyHostToDevice, s));
-  CU(cudaMemcpyAsync(c->d_base.p, base, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
-  CU(cudaEventRecord(c->ev[0], s));
-  CU(cudaMemsetAsync(c->d_state.p, 0, sizeof(CState) * (size_t)n, s));
-  CU(cudaMemsetAsync(c->d_desc.p, 0, sizeof(unsigned long long) * (size_t)items, s));
-  CU(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(BatchCtl) * 2, s));
-  CU(cudaMemcpyAsync(c->d_ctl.p, &base[n], sizeof(int32_t), cudaMemcpyHostToDevice, s));  // ctl[0].total_items
-  CU(cudaEventRecord(c->ev[1], s));
+  if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  if (int rc = L.d_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+  if (int rc = L.d_state.ensure(sizeof(CState) * (size_t)n)) return rc;
+  if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (int rc = L.d_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
+  if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
+  if (int rc = L.d_desc.ensure(sizeof(unsigned long long) * (size_t)items)) return rc;
+  if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(L.d_cinfo.p, ci, sizeof(CInfo) * (size_t)n, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(L.d_base.p, base, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(L.ev[0], s));
+  CU(cudaMemsetAsync(L.d_state.p, 0, sizeof(CState) * (size_t)n, s));
+  CU(cudaMemsetAsync(L.d_desc.p, 0, sizeof(unsigned long long) * (size_t)items, s));
+  CU(cudaMemsetAsync(L.d_ctl.p, 0, sizeof(BatchCtl) * 2, s));
+  CU(cudaMemcpyAsync(L.d_ctl.p, &base[n], sizeof(int32_t), cudaMemcpyHostToDevice, s));  // ctl[0].total_items
+  CU(cudaEventRecord(L.ev[1], s));
   CompressArgs ca;
-  ca.chunks = (const DChunk*)c->d_chunks.p;
-  ca.info = (const CInfo*)c->d_cinfo.p;
-  ca.state = (CState*)c->d_state.p;
-  ca.base = (const int32_t*)c->d_base.p;
-  ca.ctl = (BatchCtl*)c->d_ctl.p;
-  ca.desc = (unsigned long long*)c->d_desc.p;
-  ca.slab = (uint8_t*)c->d_slab.p;
+  ca.chunks = (const DChunk*)L.d_chunks.p;
+  ca.info = (const CInfo*)L.d_cinfo.p;
+  ca.state = (CState*)L.d_state.p;
+  ca.base = (const int32_t*)L.d_base.p;
+  ca.ctl = (BatchCtl*)L.d_ctl.p;
+  ca.desc = (unsigned long long*)L.d_desc.p;
+  ca.slab = (uint8_t*)L.d_slab.p;
   ca.slab_stride = (int64_t)slab_stride(c);
   ca.n = n;
   ca.win_bytes = c->cwin_bytes;
@@ -269,7 +286,7 @@ int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, in
   fa.chunks = ca.chunks;
   fa.info = ca.info;
   fa.state = ca.state;
-  fa.res = (DResult*)c->d_res.p;
+  fa.res = (DResult*)L.d_res.p;
   fa.base = ca.base;
   fa.n = n;
   fa.total_items = (int32_t)items;
@@ -277,22 +294,23 @@ int enqueue_compress(b2g_ctx* c, const DChunk* h_desc, const int32_t* nbytes, in
   const int fgrid = (int)std::min<int64_t>((int64_t)c->sms * 16, items);
   k_finalize<<<fgrid, kCtaThreads, 0, s>>>(fa);
   c->launches++;
-  CU(cudaEventRecord(c->ev[2], s));
+  CU(cudaEventRecord(L.ev[2], s));
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(c->h_res.p, c->d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(L.h_res.p, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaEventRecord(L.res_ready, s));
   return 0;
 }
 
-int finish(b2g_ctx* c, b2g_chunk* chunks, int n, cudaStream_t s) {
-  CU(cudaStreamSynchronize(s));
-  const DResult* r = (const DResult*)c->h_res.p;
+int finish(b2g_ctx* c, Lane& L, b2g_chunk* chunks, int n) {
+  CU(cudaEventSynchronize(L.res_ready));
+  const DResult* r = (const DResult*)L.h_res.p;
   for (int i = 0; i < n; i++) {
     chunks[i].status = r[i].status;
     chunks[i].out_bytes = r[i].status < 0 ? 0 : r[i].out_bytes;
   }
   float a = 0, b = 0;
-  if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) c->last_ms[0] = a;
-  if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) c->last_ms[1] = b;
+  if (cudaEventElapsedTime(&a, L.ev[0], L.ev[1]) == cudaSuccess) c->last_ms[0] += a;
+  if (cudaEventElapsedTime(&b, L.ev[1], L.ev[2]) == cudaSuccess) c->last_ms[1] += b;
   return 0;
 }
 
@@ -320,9 +338,13 @@ b2g_ctx* b2g_create(const b2g_params* params) {
   if (dev < 0 && cuda_fail(cudaGetDevice(&dev), "cudaGetDevice")) { delete c; return nullptr; }
   c->dev = dev;
   bool ok = !cuda_fail(cudaSetDevice(dev), "cudaSetDevice") &&
-            !cuda_fail(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev), "sm count") &&
-            !cuda_fail(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate");
-  for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&c->ev[i]), "cudaEventCreate");
+            !cuda_fail(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev), "sm count");
+  for (int l = 0; ok && l < kLanes; l++) {
+    Lane& L = c->lanes[l];
+    ok = !cuda_fail(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&L.ev[i]), "cudaEventCreate");
+    if (ok) ok = !cuda_fail(cudaEventCreateWithFlags(&L.res_ready, cudaEventDisableTiming), "cudaEventCreate");
+  }
   if (ok) ok = set_compress_geometry(c) == 0;
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;
   if (!ok) { b2g_destroy(c); return nullptr; }
@@ -332,13 +354,10 @@ b2g_ctx* b2g_create(const b2g_params* params) {
 void b2g_destroy(b2g_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->dev);
-  if (c->stream) cudaStreamSynchronize(c->stream);
-  for (DevBuf* b : {&c->d_chunks, &c->d_info, &c->d_res, &c->d_base, &c->d_ctl, &c->d_cinfo, &c->d_state, &c->d_desc,
-                    &c->d_slab, &c->d_in, &c->d_out})
-    b->release();
-  for (HostBuf* b : {&c->h_chunks, &c->h_res, &c->h_cinfo, &c->h_base}) b->release();
-  for (auto& e : c->ev) if (e) cudaEventDestroy(e);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  for (Lane& L : c->lanes) if (L.stream) cudaStreamSynchronize(L.stream);
+  for (Lane& L : c->lanes) L.release();
+  c->d_in.release();
+  c->d_out.release();
   delete c;
 }
 
@@ -346,18 +365,20 @@ int b2g_decompress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
   if (int rc = use_device(c)) return rc;
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->lanes[0].stream;
+  Lane& L = c->lanes[0];
   c->pend = chunks; c->pend_n = n; c->pend_stream = s;
+  c->last_ms[0] = c->last_ms[1] = 0;
   if (n == 0) return 0;
-  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n)) { c->pend = nullptr; return rc; }
-  DChunk* h = (DChunk*)c->h_chunks.p;
+  if (int rc = L.h_chunks.ensure(sizeof(DChunk) * (size_t)n)) { c->pend = nullptr; return rc; }
+  DChunk* h = (DChunk*)L.h_chunks.p;
   for (int i = 0; i < n; i++) {
     h[i].src = (const uint8_t*)chunks[i].src;
     h[i].dst = (uint8_t*)chunks[i].dst;
     h[i].src_bytes = chunks[i].src_bytes;
     h[i].dst_cap = chunks[i].dst_capacity;
   }
-  int rc = enqueue_decode(c, h, n, s, c->p.codec == B2G_ZSTD);
+  int rc = enqueue_decode(c, L, h, n, s, c->p.codec == B2G_ZSTD);
   if (rc) c->pend = nullptr;
   return rc;
 }
@@ -366,11 +387,13 @@ int b2g_compress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_s
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
   if (int rc = use_device(c)) return rc;
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->lanes[0].stream;
+  Lane& L = c->lanes[0];
   c->pend = chunks; c->pend_n = n; c->pend_stream = s;
+  c->last_ms[0] = c->last_ms[1] = 0;
   if (n == 0) return 0;
-  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n + sizeof(int32_t) * (size_t)n)) { c->pend = nullptr; return rc; }
-  DChunk* h = (DChunk*)c->h_chunks.p;
+  if (int rc = L.h_chunks.ensure(sizeof(DChunk) * (size_t)n + sizeof(int32_t) * (size_t)n)) { c->pend = nullptr; return rc; }
+  DChunk* h = (DChunk*)L.h_chunks.p;
   int32_t* nb = (int32_t*)(h + n);
   for (int i = 0; i < n; i++) {
     h[i].src = (const uint8_t*)chunks[i].src;
@@ -379,7 +402,7 @@ int b2g_compress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_s
     h[i].dst_cap = chunks[i].dst_capacity;
     nb[i] = chunks[i].src_bytes;
   }
-  int rc = enqueue_compress(c, h, nb, n, s);
+  int rc = enqueue_compress(c, L, h, nb, n, s);
   if (rc) c->pend = nullptr;
   return rc;
 }
@@ -392,7 +415,7 @@ int b2g_wait(b2g_ctx* c) {
   int n = c->pend_n;
   c->pend = nullptr;
   if (n == 0) return 0;
-  return finish(c, chunks, n, c->pend_stream);
+  return finish(c, c->lanes[0], chunks, n);
 }
 
 int b2g_chunk_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes, int32_t* blocksize) {
@@ -413,15 +436,32 @@ int b2g_chunk_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes, int32_t
   return rc;
 }
 
+// Host-pointer calls are pipelined: the batch is cut into sub-batches of about B2G_SUBBATCH_MB (default 32) MiB of
+// payload which rotate over the context's lanes, so the H2D copies of one sub-batch overlap the kernels of the previous
+// one and the D2H copies of the one before (PCIe is full duplex; the copy engines and the SMs run concurrently).
+static std::vector<int> split_batch(const std::vector<size_t>& payload) {
+  static const size_t target = [] {
+    const char* e = getenv("B2G_SUBBATCH_MB");
+    long mb = e ? atol(e) : 32;
+    return (size_t)std::max(mb, 1L) << 20;
+  }();
+  std::vector<int> bounds{0};
+  size_t acc = 0;
+  for (int i = 0; i < (int)payload.size(); i++) {
+    acc += payload[i];
+    if (acc >= target || i + 1 - bounds.back() >= 65536) { bounds.push_back(i + 1); acc = 0; }
+  }
+  if (bounds.back() != (int)payload.size()) bounds.push_back((int)payload.size());
+  return bounds;
+}
+
 int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
   if (n == 0) return 0;
   if (int rc = use_device(c)) return rc;
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
-  DChunk* h = (DChunk*)c->h_chunks.p;
-  std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n);
+  (void)cuda_stream;  // the call returns when the data is back in host memory; it runs on the context's own lanes
+  std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n), payload(n);
   size_t in_total = 0, out_total = 0;
   int maxblock = 0;
   bool any_zstd = false;
@@ -442,22 +482,40 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
     }
     in_off[i] = in_total; in_len[i] = take; in_total += align_up(take + 8, 256);
     out_off[i] = out_total; out_len[i] = give; out_total += align_up(give + 8, 256);
+    payload[i] = take + give;
   }
   if (int rc = set_geometry(c, std::max(maxblock, c->blocksize))) return rc;
   if (int rc = c->d_in.ensure(in_total + 256)) return rc;
   if (int rc = c->d_out.ensure(out_total + 256)) return rc;
-  for (int i = 0; i < n; i++) {
-    h[i].src = (const uint8_t*)c->d_in.p + in_off[i];
-    h[i].dst = (uint8_t*)c->d_out.p + out_off[i];
-    h[i].src_bytes = chunks[i].src_bytes == INT32_MAX ? (int32_t)in_len[i] : std::min<int32_t>(chunks[i].src_bytes, (int32_t)in_len[i]);
-    h[i].dst_cap = chunks[i].dst_capacity;
-    if (in_len[i])
-      CU(cudaMemcpyAsync((void*)h[i].src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
+  c->last_ms[0] = c->last_ms[1] = 0;
+  const std::vector<int> bounds = split_batch(payload);
+  const int nsub = (int)bounds.size() - 1;
+  for (int k = 0; k < nsub + kLanes; k++) {
+    Lane& L = c->lanes[k % kLanes];
+    if (k >= kLanes) {  // retire the sub-batch that used this lane last
+      const int lo = bounds[k - kLanes], cnt = bounds[k - kLanes + 1] - lo;
+      if (int rc = finish(c, L, chunks + lo, cnt)) return rc;
+    }
+    if (k >= nsub) continue;
+    const int lo = bounds[k], cnt = bounds[k + 1] - lo;
+    cudaStream_t s = L.stream;
+    if (int rc = L.h_chunks.ensure(sizeof(DChunk) * (size_t)cnt)) return rc;
+    DChunk* h = (DChunk*)L.h_chunks.p;
+    for (int i = lo; i < lo + cnt; i++) {
+      DChunk& d = h[i - lo];
+      d.src = (const uint8_t*)c->d_in.p + in_off[i];
+      d.dst = (uint8_t*)c->d_out.p + out_off[i];
+      d.src_bytes = chunks[i].src_bytes == INT32_MAX ? (int32_t)in_len[i]
+                                                     : std::min<int32_t>(chunks[i].src_bytes, (int32_t)in_len[i]);
+      d.dst_cap = chunks[i].dst_capacity;
+      if (in_len[i]) CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
+    }
+    if (int rc = enqueue_decode(c, L, h, cnt, s, any_zstd)) return rc;
+    for (int i = lo; i < lo + cnt; i++)
+      if (out_len[i]) CU(cudaMemcpyAsync(chunks[i].dst, h[i - lo].dst, out_len[i], cudaMemcpyDeviceToHost, s));
   }
-  if (int rc = enqueue_decode(c, h, n, s, any_zstd)) return rc;
-  for (int i = 0; i < n; i++)
-    if (out_len[i]) CU(cudaMemcpyAsync(chunks[i].dst, h[i].dst, out_len[i], cudaMemcpyDeviceToHost, s));
-  return finish(c, chunks, n, s);
+  for (Lane& L : c->lanes) CU(cudaStreamSynchronize(L.stream));
+  return 0;
 }
 
 int b2g_compress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
@@ -465,35 +523,50 @@ int b2g_compress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) 
   if (c->pend) return B2G_ERR_FAILURE;
   if (n == 0) return 0;
   if (int rc = use_device(c)) return rc;
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-  if (int rc = c->h_chunks.ensure(sizeof(DChunk) * (size_t)n + sizeof(int32_t) * (size_t)n)) return rc;
-  DChunk* h = (DChunk*)c->h_chunks.p;
-  int32_t* nb = (int32_t*)(h + n);
-  std::vector<size_t> in_off(n), out_off(n);
+  (void)cuda_stream;
+  std::vector<size_t> in_off(n), out_off(n), payload(n);
   size_t in_total = 0, out_total = 0;
   for (int i = 0; i < n; i++) {
     const int32_t sz = std::max(chunks[i].src_bytes, 0);
     const int32_t cap = std::max(std::min(chunks[i].dst_capacity, sz + B2G_MAX_OVERHEAD), 0);
     in_off[i] = in_total; in_total += align_up((size_t)sz + 8, 256);
     out_off[i] = out_total; out_total += align_up((size_t)cap + 8, 256);
+    payload[i] = (size_t)sz;
   }
   if (int rc = c->d_in.ensure(in_total + 256)) return rc;
   if (int rc = c->d_out.ensure(out_total + 256)) return rc;
-  for (int i = 0; i < n; i++) {
-    h[i].src = (const uint8_t*)c->d_in.p + in_off[i];
-    h[i].dst = (uint8_t*)c->d_out.p + out_off[i];
-    h[i].src_bytes = chunks[i].src_bytes;
-    h[i].dst_cap = std::min(chunks[i].dst_capacity, std::max(chunks[i].src_bytes, 0) + B2G_MAX_OVERHEAD);
-    nb[i] = chunks[i].src_bytes;
-    if (chunks[i].src_bytes > 0)
-      CU(cudaMemcpyAsync((void*)h[i].src, chunks[i].src, (size_t)chunks[i].src_bytes, cudaMemcpyHostToDevice, s));
+  c->last_ms[0] = c->last_ms[1] = 0;
+  const std::vector<int> bounds = split_batch(payload);
+  const int nsub = (int)bounds.size() - 1;
+  for (int k = 0; k < nsub + kLanes; k++) {
+    Lane& L = c->lanes[k % kLanes];
+    if (k >= kLanes) {  // retire: the sizes are needed before the chunks can be copied back
+      const int lo = bounds[k - kLanes], cnt = bounds[k - kLanes + 1] - lo;
+      if (int rc = finish(c, L, chunks + lo, cnt)) return rc;
+      for (int i = lo; i < lo + cnt; i++)
+        if (chunks[i].out_bytes > 0)
+          CU(cudaMemcpyAsync(chunks[i].dst, (uint8_t*)c->d_out.p + out_off[i], (size_t)chunks[i].out_bytes,
+                             cudaMemcpyDeviceToHost, L.stream));
+    }
+    if (k >= nsub) continue;
+    const int lo = bounds[k], cnt = bounds[k + 1] - lo;
+    cudaStream_t s = L.stream;
+    if (int rc = L.h_chunks.ensure((sizeof(DChunk) + sizeof(int32_t)) * (size_t)cnt)) return rc;
+    DChunk* h = (DChunk*)L.h_chunks.p;
+    int32_t* nb = (int32_t*)(h + cnt);
+    for (int i = lo; i < lo + cnt; i++) {
+      DChunk& d = h[i - lo];
+      d.src = (const uint8_t*)c->d_in.p + in_off[i];
+      d.dst = (uint8_t*)c->d_out.p + out_off[i];
+      d.src_bytes = chunks[i].src_bytes;
+      d.dst_cap = std::min(chunks[i].dst_capacity, std::max(chunks[i].src_bytes, 0) + B2G_MAX_OVERHEAD);
+      nb[i - lo] = chunks[i].src_bytes;
+      if (chunks[i].src_bytes > 0)
+        CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, (size_t)chunks[i].src_bytes, cudaMemcpyHostToDevice, s));
+    }
+    if (int rc = enqueue_compress(c, L, h, nb, cnt, s)) return rc;
   }
-  if (int rc = enqueue_compress(c, h, nb, n, s)) return rc;
-  if (int rc = finish(c, chunks, n, s)) return rc;  // sizes are needed before the chunks can be copied back
-  for (int i = 0; i < n; i++)
-    if (chunks[i].out_bytes > 0)
-      CU(cudaMemcpyAsync(chunks[i].dst, h[i].dst, (size_t)chunks[i].out_bytes, cudaMemcpyDeviceToHost, s));
-  CU(cudaStreamSynchronize(s));
+  for (Lane& L : c->lanes) CU(cudaStreamSynchronize(L.stream));
   return 0;
 }
 
@@ -505,7 +578,7 @@ int b2g_filter_device(b2g_ctx* c, int filter, int forward, int typesize, int for
   if (int rc = use_device(c)) return rc;
   if (int rc = set_geometry(c, blocksize)) return rc;
   if (blocksize > c->win_bytes) return B2G_ERR_BLOCKSIZE;
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->lanes[0].stream;
   FilterArgs fa;
   fa.src = (const uint8_t*)src;
   fa.dst = (uint8_t*)dst;
