@@ -89,37 +89,53 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
   for (int tbase = 0; tbase <= plimit; tbase += kEncTile) {
     if (ip >= tbase + kEncTile) continue;  // the tile lies inside an earlier match
     // ---- phase 1: candidates ----------------------------------------------------------------------------------
+    // Four groups of 32 positions per step, as four independent dependency chains (the step is latency-bound, not
+    // issue-bound).  Within a step every position sees the table as it was before the step plus the earlier positions
+    // of its own group; a first occurrence 32..127 bytes back inside the same step is the only candidate missed.
     unsigned myflags = 0;
-    for (int g = 0; g < 32; g++) {
-      const int gbase = tbase + g * 32;
-      if (gbase > plimit) break;
-      if (gbase + 31 < ip) continue;
-      if (step > 1 && (g & (step - 1))) continue;
-      const int p = gbase + lane;
-      const bool live = p <= plimit;
-      uint32_t seq = 0, h = 0x80000000u | (uint32_t)lane;  // dead lanes get unique keys
-      if (live) {
-        seq = ld32_any(in + p);
-        h = (seq * 2654435761u) >> (32 - w.hlog);
+    for (int gb = 0; gb < 32; gb += 4) {
+      const int bbase = tbase + gb * 32;
+      if (bbase > plimit) break;
+      if (bbase + 127 < ip) continue;
+      if (step > 1 && ((gb >> 2) & (step - 1))) continue;
+      uint32_t seq[4], h[4], tab[4];
+      unsigned peers[4];
+      bool live[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int p = bbase + 32 * j + lane;
+        live[j] = p <= plimit;
+        seq[j] = ld32_any(in + (live[j] ? p : 0));
+        h[j] = (seq[j] * 2654435761u) >> (32 - w.hlog);
+        tab[j] = w.htab[h[j]];
       }
-      const unsigned peers = match_any_u32(h);
-      const unsigned prev = peers & lt_mask;
-      const int src = prev ? 31 - __clz((int)prev) : lane;
-      const uint32_t pseq = __shfl_sync(kFull, seq, src);
-      int c = -1;
-      bool ok;
-      if (prev) {  // the most recent earlier position with this hash is in this very step
-        c = gbase + src;
-        ok = live && pseq == seq;
-      } else {
-        if (live) c = p - (int)((uint32_t)(p - (int)w.htab[h]) & 0xffffu);
-        ok = live && c >= 0 && c < p && ld32_any(in + c) == seq;
+#pragma unroll
+      for (int j = 0; j < 4; j++) peers[j] = match_any_u32(live[j] ? h[j] : (0x80000000u | (uint32_t)lane));
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int p = bbase + 32 * j + lane;
+        const unsigned prev = peers[j] & lt_mask;
+        const int src = prev ? 31 - __clz((int)prev) : lane;
+        const uint32_t pseq = __shfl_sync(kFull, seq[j], src);
+        int c = p - (int)((uint32_t)(p - (int)tab[j]) & 0xffffu);   // table candidate, within 65535 of p
+        const bool tab_ok = c >= 0 && c < p;
+        const uint32_t cseq = ld32_any(in + (tab_ok ? c : 0));
+        bool ok;
+        if (prev) {  // the most recent earlier position with this hash is in this very group
+          c = bbase + 32 * j + src;
+          ok = live[j] && pseq == seq[j];
+        } else {
+          ok = live[j] && tab_ok && cseq == seq[j];
+        }
+        w.off[(gb + j) * 32 + lane] = ok ? (uint16_t)(p - c) : (uint16_t)0;
+        const unsigned fl = __ballot_sync(kFull, ok);
+        if (lane == gb + j) myflags = fl;
       }
       __syncwarp();  // every table read of the step happens before any table write
-      if (live && (peers >> lane) == 1u) w.htab[h] = (uint16_t)p;  // last position of each hash group
-      w.off[g * 32 + lane] = ok ? (uint16_t)(p - c) : (uint16_t)0;
-      const unsigned fl = __ballot_sync(kFull, ok);
-      if (lane == g) myflags = fl;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (live[j] && (peers[j] >> lane) == 1u) w.htab[h[j]] = (uint16_t)(bbase + 32 * j + lane);  // last of its hash group
+      __syncwarp();  // ... and every write before the next step's reads
     }
     __syncwarp();
     // ---- phase 2: greedy parse ------------------------------------------------------------------------------------
