@@ -66,7 +66,6 @@ struct HostBuf {  // pinned
 };
 
 constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
-constexpr size_t kDecodeSharedBytes = 256;  // DecodeShared, padded
 constexpr size_t kCompressSharedBytes = 256;
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -99,13 +98,15 @@ struct b2g_ctx {
   float last_ms[2] = {0, 0};
   int64_t launches = 0;
   // geometry
-  int blocksize = 32768;   // context blocksize (compress) / largest block the device decode path is sized for
-  int win_bytes = 32768;   // shared-memory window (decode, filters)
+  int blocksize = 32768;   // context blocksize (compress) / largest block the decode path is sized for (slab, plan)
+  int stream_hint = 32768; // stream size the decode windows are sized for on the device-resident path
+  int win_bytes = 32768;   // shared-memory window (standalone filters)
   int cwin_bytes = 32768;  // shared-memory window (compress)
-  size_t dec_smem = 0, decz_smem = 0, comp_smem = 0;
-  int dec_grid = 0, decz_grid = 0, comp_grid = 0;
-  int dec_threads = kCtaThreads, comp_threads = kCtaThreads;  // 32 x streams per block (<= kCtaWarps warps)
-  int htab_bytes = 4096;                                      // per-warp encoder hash table
+  size_t comp_smem = 0;
+  int comp_grid = 0;
+  int comp_threads = kCtaThreads;  // 32 x streams per block (<= kCtaWarps warps)
+  int htab_bytes = 4096;           // per-warp encoder hash table
+  int max_grid_warps = 0;          // most decode warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
   // device + pinned work buffers
   DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
@@ -150,38 +151,63 @@ int set_compress_geometry(b2g_ctx* c) {
   return 0;
 }
 
-// Decode geometry: (re)derived for the largest blocksize seen so far (host-pointer calls read it from the headers).
+// Largest blocksize seen so far: bounds the global-slab windows and the standalone-filter window.
 int set_geometry(b2g_ctx* c, int blocksize) {
   if (c->geometry_ready && blocksize <= c->blocksize) return 0;
   c->blocksize = std::max(blocksize, 1);
   const int win = (int)align_up((size_t)std::min(c->blocksize, kMaxSmemWindow), 16);
   c->win_bytes = std::max(win, 1024);
-  c->dec_smem = (size_t)c->win_bytes + kDecodeSharedBytes;
-  c->decz_smem = (size_t)c->win_bytes + kDecodeSharedBytes + sizeof(ZWork) * kCtaWarps;
-  // CTA width: one warp per stream; the context's typesize is the hint for the chunks it will see (any chunk still
-  // decodes: a warp then takes several streams in turn)
-  c->dec_threads = 32 * plan_cta_warps(c->p.typesize <= kMaxStreams ? c->p.typesize : 1);
   // The dynamic shared-memory limit is a per-function (per-device) attribute shared by every context of the process:
   // only ever raise it, or a context sized for small blocks would cut off one sized for large blocks.
-  if (int rc = raise_smem_limit(c->dev, 0, (const void*)k_decode<false>, c->dec_smem)) return rc;
-  if (int rc = raise_smem_limit(c->dev, 1, (const void*)k_decode<true>, c->decz_smem)) return rc;
   if (int rc = raise_smem_limit(c->dev, 3, (const void*)k_filter, (size_t)c->win_bytes)) return rc;
-  int occ = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, c->dec_threads, c->dec_smem));
-  c->dec_grid = c->sms * std::max(occ, 1);
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, c->dec_threads, c->decz_smem));
-  c->decz_grid = c->sms * std::max(occ, 1);
   c->geometry_ready = true;
   return 0;
 }
 
 size_t slab_stride(const b2g_ctx* c) {
-  return align_up((size_t)std::max(c->blocksize, c->p.blocksize) + 16 * kMaxStreams + 256, 256);
+  return align_up((size_t)decode_window_bytes(std::max(c->blocksize, c->p.blocksize)) + 256, 256);
 }
 
-int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd) {
-  // slab: whole blocks for decode blocks larger than the shared window, one per CTA
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid)))) return rc;
+// Decode launch geometry for streams of `stream_bytes`: every warp is an independent worker with its own window, so
+// the CTA shape only matters for how many warps fit an SM's shared memory (228 KiB, 1 KiB reserved per CTA).
+struct DecGeom {
+  int wcap, wstride, warps, grid;
+  size_t smem;
+};
+int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
+  if (stream_bytes > 96 * 1024) stream_bytes = 16 * 1024;  // such streams decode through the global slab anyway
+  g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1)), 1024);
+  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : 0);
+  int best = 0;
+  g.warps = 1;
+  for (int w : {1, 2, 3, 4, 6, 8}) {
+    const size_t cta = (size_t)w * g.wstride;
+    if (cta > 227 * 1024) break;
+    int n = (int)((228 * 1024) / (cta + 1024));
+    n = std::min(n, std::min(32, 64 / w));
+    if (w * n >= best) { best = w * n; g.warps = w; }
+  }
+  g.smem = (size_t)g.warps * g.wstride;
+  const void* fn = zstd ? (const void*)k_decode<true> : (const void*)k_decode<false>;
+  if (int rc = raise_smem_limit(c->dev, zstd ? 1 : 0, fn, g.smem)) return rc;
+  int occ = 0;
+  if (zstd) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<true>, 32 * g.warps, g.smem));
+  else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_decode<false>, 32 * g.warps, g.smem));
+  g.grid = c->sms * std::max(occ, 1);
+  // the slab holds one window per warp of the grid: keep it below 1 GiB for very large blocks
+  const size_t max_warps = std::max((size_t)c->sms, ((size_t)1 << 30) / slab_stride(c));
+  g.grid = (int)std::min<size_t>((size_t)g.grid, std::max<size_t>(max_warps / g.warps, 1));
+  return 0;
+}
+
+int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd, int stream_bytes) {
+  DecGeom g, gz;
+  if (int rc = decode_geometry(c, stream_bytes, false, g)) return rc;
+  gz = g;
+  if (want_zstd) if (int rc = decode_geometry(c, stream_bytes, true, gz)) return rc;
+  // slab: windows for streams larger than the shared-memory window, one per warp of the grid
+  c->max_grid_warps = std::max(c->max_grid_warps, std::max(g.grid * g.warps, gz.grid * gz.warps));
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, c->max_grid_warps))) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = L.d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
@@ -197,7 +223,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   pa.base = (int32_t*)L.d_base.p;
   pa.ctl = (BatchCtl*)L.d_ctl.p;
   pa.n = n;
-  pa.max_block = c->blocksize;
+  pa.max_block = std::max(c->blocksize, c->p.blocksize);
   pa.zstd_ok = want_zstd ? 1 : 0;
   k_plan_decode<<<1, 1024, 2 * 1024 * sizeof(int32_t), s>>>(pa);
   c->launches++;
@@ -209,15 +235,18 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.base = pa.base;
   da.ctl = pa.ctl;
   da.n = n;
-  da.win_bytes = c->win_bytes;
+  da.wcap = g.wcap;
+  da.wstride = g.wstride;
   da.slab = (uint8_t*)L.d_slab.p;
   da.slab_stride = (int64_t)slab_stride(c);
-  k_decode<false><<<c->dec_grid, c->dec_threads, c->dec_smem, s>>>(da);
+  k_decode<false><<<g.grid, 32 * g.warps, g.smem, s>>>(da);
   c->launches++;
   if (want_zstd) {
     da.base = pa.base + (n + 1);
     da.ctl = pa.ctl + 1;
-    k_decode<true><<<c->decz_grid, c->dec_threads, c->decz_smem, s>>>(da);
+    da.wcap = gz.wcap;
+    da.wstride = gz.wstride;
+    k_decode<true><<<gz.grid, 32 * gz.warps, gz.smem, s>>>(da);
     c->launches++;
   }
   CU(cudaEventRecord(L.ev[2], s));
@@ -228,7 +257,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
 }
 
 int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, std::max(c->dec_grid, c->decz_grid)))) return rc;
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, c->max_grid_warps))) return rc;
   const b2g_params& p = c->p;
   if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
   if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
@@ -345,6 +374,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
     for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&L.ev[i]), "cudaEventCreate");
     if (ok) ok = !cuda_fail(cudaEventCreateWithFlags(&L.res_ready, cudaEventDisableTiming), "cudaEventCreate");
   }
+  c->stream_hint = c->p.blocksize / plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, c->p.blocksize);
   if (ok) ok = set_compress_geometry(c) == 0;
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;
   if (!ok) { b2g_destroy(c); return nullptr; }
@@ -378,7 +408,7 @@ int b2g_decompress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda
     h[i].src_bytes = chunks[i].src_bytes;
     h[i].dst_cap = chunks[i].dst_capacity;
   }
-  int rc = enqueue_decode(c, L, h, n, s, c->p.codec == B2G_ZSTD);
+  int rc = enqueue_decode(c, L, h, n, s, c->p.codec == B2G_ZSTD, c->stream_hint);
   if (rc) c->pend = nullptr;
   return rc;
 }
@@ -463,7 +493,7 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
   (void)cuda_stream;  // the call returns when the data is back in host memory; it runs on the context's own lanes
   std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n), payload(n);
   size_t in_total = 0, out_total = 0;
-  int maxblock = 0;
+  int maxblock = 0, maxstream = 0;
   bool any_zstd = false;
   for (int i = 0; i < n; i++) {
     const uint8_t* src = (const uint8_t*)chunks[i].src;
@@ -475,7 +505,12 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
       take = (size_t)std::max(kHdrMin, std::min(avail, cb < kHdrMin ? kHdrExt : cb));  // INT32_MAX: trust the header
       if (avail != INT32_MAX) take = std::min(take, (size_t)avail);
       if (nb > 0 && nb <= chunks[i].dst_capacity) give = (size_t)nb;
-      if (bs > 0 && bs <= kMaxBlocksize) maxblock = std::max(maxblock, bs);
+      if (bs > 0 && bs <= kMaxBlocksize) {
+        maxblock = std::max(maxblock, bs);
+        const int ts = src[3];  // split blocks are stored as `typesize` streams (flag bit 4 clear)
+        const bool split = !(src[2] & kFlagDontSplit) && !(src[2] & kFlagMemcpyed) && ts >= 1 && ts <= kMaxStreams;
+        maxstream = std::max(maxstream, split ? bs / ts : bs);
+      }
       if ((src[2] >> 5) == kFmtZstd) any_zstd = true;
     } else if (src && avail > 0) {
       take = (size_t)avail;
@@ -510,7 +545,7 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
       d.dst_cap = chunks[i].dst_capacity;
       if (in_len[i]) CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
     }
-    if (int rc = enqueue_decode(c, L, h, cnt, s, any_zstd)) return rc;
+    if (int rc = enqueue_decode(c, L, h, cnt, s, any_zstd, std::max(maxstream, 1))) return rc;
     for (int i = lo; i < lo + cnt; i++)
       if (out_len[i]) CU(cudaMemcpyAsync(chunks[i].dst, h[i - lo].dst, out_len[i], cudaMemcpyDeviceToHost, s));
   }

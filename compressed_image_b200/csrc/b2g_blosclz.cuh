@@ -14,7 +14,9 @@ namespace b2g {
 constexpr int kBlzMaxDistance = 8191;
 
 // Decodes in[0..n) into out[0..cap).  Returns the decoded size, 0 on any error (as the reference does).
-__device__ __forceinline__ int blosclz_decode_warp(const uint8_t* in, int n, uint8_t* out, int cap) {
+// INPLACE: in == out + a (see lz4_decode_warp_t); -2 = the output would pass unread input, decode from the original.
+template <bool INPLACE>
+__device__ __forceinline__ int blosclz_decode_warp_t(const uint8_t* in, int n, uint8_t* out, int cap, int a) {
   const int lane = lane_id();
   if (n <= 0) return 0;
   int ip = 0, op = 0;
@@ -41,6 +43,7 @@ __device__ __forceinline__ int blosclz_decode_warp(const uint8_t* in, int n, uin
       if (op - dist - 1 < 0) return 0;
       if (ip >= n) break;  // a trailing match is NOT copied (blosclz.c:742)
       ctrl = in[ip++];
+      if (INPLACE && op + len > a + ip) return -2;
       __syncwarp();
       lz_match_copy(out, op, dist + 1, len, lane);
       op += len;
@@ -48,15 +51,21 @@ __device__ __forceinline__ int blosclz_decode_warp(const uint8_t* in, int n, uin
       const int run = (int)ctrl + 1;
       if (op + run > cap) return 0;
       if (ip + run > n) return 0;
-      if (lane < run) out[op + lane] = in[ip + lane];
+      const uint32_t nctrl = ip + run < n ? in[ip + run] : 0u;  // read before the run is written: in place, the run
+      lz_literal_copy<INPLACE>(out, op, in, ip, run, a + ip - op, lane);  // may end right below it
       op += run;
       ip += run;
       if (ip >= n) break;
-      ctrl = in[ip++];
+      ctrl = nctrl;
+      ip++;
     }
   }
   __syncwarp();
   return op;
+}
+
+__device__ __forceinline__ int blosclz_decode_warp(const uint8_t* in, int n, uint8_t* out, int cap) {
+  return blosclz_decode_warp_t<false>(in, n, out, cap, 0);
 }
 
 // Literal runs: `lit` bytes from in[anchor..] as chained groups of (control byte, <= 32 literals).

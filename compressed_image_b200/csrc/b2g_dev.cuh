@@ -42,9 +42,10 @@ struct DChunk {
 struct DInfo {
   int32_t nbytes, blocksize, cbytes, nblocks, leftover;
   int32_t item_base;     // first work item (= block) of this chunk in the batch-wide item numbering
-  int32_t nitems;        // blocks to decode (0 for chunks fully handled by the plan kernel / failed chunks)
+  int32_t nitems;        // work items: streams (blocks for special / memcpyed chunks); 0 for empty / failed chunks
   int32_t vts;           // special "repeated value" chunks: size of the value (cbytes - 32)
-  uint8_t version, flags, typesize, filter, fmt, dont_split, special, memcpyed, hdr, pad[3];
+  int32_t nstreams;      // streams a full block is stored as (typesize when split, else 1)
+  uint8_t version, flags, typesize, filter, fmt, dont_split, special, memcpyed, hdr, cls, serial, pad;
 };
 
 // Result of a batch, per chunk (device -> host).

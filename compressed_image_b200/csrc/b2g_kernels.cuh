@@ -1,11 +1,12 @@
 // b2g_kernels.cuh -- the batch kernels of the b2g engine (sm_100a).
 //
 //   k_plan_decode   one thread per chunk: parse + validate the blosc2 header (F1/F2/F4 of SURVEY.md 8a;
-//                   blosc/blosc2.c:672-766, 2298-2391, 2922-2951), lay the batch out as work items (= blocks).
-//   k_decode<Z>     persistent CTAs pull block items from a ticket; per block: stream directory, one warp per stream
-//                   (lz4 / blosclz / zstd / stored / run / zero: blosc_d, blosc2.c:1568-1937) into a shared-memory
-//                   window, then the fused un-filter writes the raw block with 128-bit stores (pipeline_backward,
-//                   blosc2.c:1336-1461).  <Z = true> adds the zstd work areas and serves only zstd chunks.
+//                   blosc/blosc2.c:672-766, 2298-2391, 2922-2951), lay the batch out as work items (= streams).
+//   k_decode<Z>     persistent independent warps pull stream items from a ticket; per stream: directory walk, the
+//                   compressed bytes staged at the top of the warp's shared-memory window and decoded in place
+//                   (lz4 / blosclz / zstd / stored / run / zero: blosc_d, blosc2.c:1568-1937), then the fused un-filter:
+//                   a byte plane is scattered into the raw block, whole-block streams are un(bit)shuffled
+//                   (pipeline_backward, blosc2.c:1336-1461).  <Z = true> adds the zstd work area; zstd chunks only.
 //   k_compress      persistent CTAs, ticket order: fused filter into the shared window (pipeline_forward,
 //                   blosc2.c:940-1050), one warp per stream (run detection blosc2.c:1054-1076, lz4 / blosclz, raw
 //                   fallback: blosc_c, blosc2.c:1080-1332) into an L2-resident per-CTA slab, decoupled look-back over
@@ -34,7 +35,7 @@ struct PlanArgs {
 __device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_block, int zstd_ok) {
   const uint8_t* src = ch.src;
   const int32_t srcsize = ch.src_bytes;
-  d.nitems = 0; d.nblocks = 0; d.nbytes = 0; d.vts = 0;
+  d.nitems = 0; d.nblocks = 0; d.nbytes = 0; d.vts = 0; d.nstreams = 1; d.serial = 0;
   if (srcsize < kHdrMin) return kErrRead;
   d.version = src[0];
   d.flags = src[2];
@@ -97,8 +98,21 @@ __device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_bloc
     if (d.fmt != kFmtBlosclz && d.fmt != kFmtLz4 && d.fmt != kFmtZstd) return kErrCodec;
     if (blocksize > max_block) return kErrBlocksize;
     if (d.fmt == kFmtZstd && !zstd_ok) return kErrCtxCodec;
+    // work items: one per stream (blosc2.c:1771-1776: a leftover block is never split)
+    const int32_t full = nblocks - (d.leftover > 0 ? 1 : 0);
+    if (!d.dont_split) {
+      if (ts <= kMaxStreams) d.nstreams = ts;
+      else if (full > 0) return kErrData;
+    }
+    // planes of a byte-shuffled block are independent work items; a split block under any other filter (Blosc1-era
+    // bitshuffle chunks) needs all its streams in one window before the un-filter: one item, streams decoded in turn
+    d.serial = (d.nstreams > 1 && d.filter != kFilterShuffle) ? 1 : 0;
+    const int per_block = d.serial ? 1 : d.nstreams;
+    if ((long long)full * per_block > (1 << 28)) return kErrMaxBuf;
+    d.nitems = full * per_block + (d.leftover > 0 ? 1 : 0);
+  } else {
+    d.nitems = nblocks;  // special-value / memcpyed chunks: one item per block
   }
-  d.nitems = nblocks;
   return 0;
 }
 
@@ -115,7 +129,7 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
     a.res[i].status = rc;
     a.res[i].out_bytes = rc < 0 ? 0 : d.nbytes;
     const int cls = (d.nitems > 0 && !d.special && !d.memcpyed && d.fmt == kFmtZstd) ? 1 : 0;
-    d.pad[0] = (uint8_t)cls;
+    d.cls = (uint8_t)cls;
     d.item_base = sum[cls];  // provisional: offset inside this thread's range
     sum[cls] += d.nitems;
     a.info[i] = d;
@@ -135,7 +149,7 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
   __syncthreads();
   int32_t off[2] = {cnt[t], cnt[nt + t]};
   for (int i = lo; i < hi; i++) {
-    const int cls = a.info[i].pad[0];
+    const int cls = a.info[i].cls;
     const int32_t nit = a.info[i].nitems;
     a.base[i] = off[0];
     a.base[(a.n + 1) + i] = off[1];
@@ -160,6 +174,11 @@ __device__ __forceinline__ int find_chunk(const int32_t* base, int n, int item, 
 }
 
 // ---- decode ----------------------------------------------------------------------------------------------------------
+// Work item = one STREAM of one block (a byte plane of a split shuffled block, or the whole block when it is stored as
+// a single stream); special-value and memcpyed chunks are laid out as one item per block.  Every warp of the grid is an
+// independent worker: it draws items from the class ticket, owns `wcap` bytes of shared memory and never waits for
+// another warp (streams of one block take very different times: a noisy low byte plane has ten times the sequences of
+// the smooth high plane).
 struct DecodeArgs {
   const DChunk* chunks;
   const DInfo* info;
@@ -167,25 +186,26 @@ struct DecodeArgs {
   const int32_t* base;   // this class's [n + 1]
   BatchCtl* ctl;         // this class's
   int32_t n;
-  int32_t win_bytes;     // shared-memory window capacity
-  uint8_t* slab;         // global scratch for blocks larger than the window: one slab per CTA
+  int32_t wcap;          // shared-memory window of one warp (bytes, multiple of 16)
+  int32_t wstride;       // bytes of shared memory per warp: wcap (+ the zstd work area)
+  uint8_t* slab;         // global scratch window for streams that do not fit in wcap: one per warp of the grid
   int64_t slab_stride;
 };
 
-struct DecodeShared {
-  int32_t item, chunk;
-  int32_t spos[kMaxStreams];    // payload offset of each stream inside the chunk
-  int32_t scsize[kMaxStreams];  // its csize field
-  int32_t err;
-};
+// Window bytes needed to decode a stream of `neblock` bytes with its compressed bytes staged in place above the output.
+__host__ __device__ __forceinline__ int decode_window_bytes(int neblock) {
+  return (neblock + (neblock >> 5) + 64 + 15) & ~15;  // blosclz literal runs expand by 1/32
+}
 
-// One stream of a block (blosc2.c:1783-1923) decoded by one warp into out[0..neblock).
-template <bool Z>
+// One stream (blosc2.c:1783-1923) decoded by one warp into win[0..neblock).  `wbytes` = usable bytes of the window:
+// lz4 / blosclz streams are first copied to its top (16-byte loads, same alignment phase as the source) and decoded in
+// place, so the byte-serial part of the decoder only ever touches the window.
+template <bool Z, bool STAGE>
 __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, int32_t csize, int32_t avail,
-                                             uint8_t* out, int32_t neblock, ZWork* zw) {
+                                             uint8_t* win, int32_t wbytes, int32_t neblock, ZWork* zw) {
   const int lane = lane_id();
   if (csize == 0) {
-    fill_bytes(out, 0, neblock, lane, 32);
+    fill_bytes(win, 0, neblock, lane, 32);
     return 0;
   }
   if (csize < 0) {
@@ -193,125 +213,146 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
     const uint8_t token = payload[0];
     if (!(token & 1)) return kErrRunLength;
     if (csize < -255) return kErrRunLength;
-    fill_bytes(out, (uint8_t)(-csize), neblock, lane, 32);
+    fill_bytes(win, (uint8_t)(-csize), neblock, lane, 32);
     return 0;
   }
   if (csize > avail) return kErrRead;
   if (csize == neblock) {
-    copy_bytes(out, payload, neblock, lane, 32);
+    copy_bytes(win, payload, neblock, lane, 32);
     return 0;
   }
   int got;
   if (Z) {
     if (fmt != kFmtZstd) return kErrCodec;
-    long r = zstd_decode_warp(zw, payload, csize, out, neblock);
+    long r = zstd_decode_warp(zw, payload, csize, win, neblock);
     got = r < 0 ? 0 : (int)r;  // blosc2.c:545-548: zstd errors surface as 0 bytes
   } else {
-    if (fmt == kFmtLz4) got = lz4_decode_warp(payload, csize, out, neblock);
-    else if (fmt == kFmtBlosclz) got = blosclz_decode_warp(payload, csize, out, neblock);
-    else return kErrCodec;
+    if (fmt != kFmtLz4 && fmt != kFmtBlosclz) return kErrCodec;
+    got = -2;
+    if (STAGE) {
+      const int m = (int)((uintptr_t)payload & 15);
+      const int a = ((wbytes - csize - m) & ~15) + m;  // a + csize <= wbytes, (win + a) = payload (mod 16)
+      if (wbytes - csize - m >= 0) {
+        copy_bytes(win + a, payload, csize, lane, 32);
+        __syncwarp();
+        got = fmt == kFmtLz4 ? lz4_decode_warp_t<true>(win + a, csize, win, neblock, a)
+                             : blosclz_decode_warp_t<true>(win + a, csize, win, neblock, a);
+      }
+    }
+    if (got == -2) {  // not staged, or the output caught up with the staged input: decode from the chunk itself
+      __syncwarp();
+      got = fmt == kFmtLz4 ? lz4_decode_warp(payload, csize, win, neblock)
+                           : blosclz_decode_warp(payload, csize, win, neblock);
+    }
   }
   return got == neblock ? 0 : kErrData;
 }
 
+// Streams [s, s_end) of one block, decoded by one warp into `win` and un-filtered into the raw block.
+struct StreamJob {
+  const uint8_t* src;   // the chunk
+  uint8_t* raw;         // the raw block
+  int32_t srcsize, first, s, s_end, ns, neblock, bsize;
+  bool scatter;
+  uint8_t fmt, filter, typesize, version;
+};
+
+template <bool Z, bool STAGE, bool SMEM>
+__device__ __forceinline__ int decode_streams(const StreamJob& jb, uint8_t* win, int32_t wbytes, ZWork* zw) {
+  const int lane = lane_id();
+  // stream directory: each csize tells where the next stream starts (warp-uniform loads)
+  int32_t pos = jb.first;
+  if (pos <= 0 || pos >= jb.srcsize) return kErrData;
+  if (jb.neblock == 0) return kErrWrite;
+  for (int k = 0; k < jb.s_end; k++) {
+    if (jb.srcsize - pos < 4) return kErrRead;
+    const int32_t cs = ld_le32(jb.src + pos);
+    pos += 4;
+    if (cs > 0 && jb.srcsize - pos < cs) return kErrRead;
+    if (cs < 0 && jb.srcsize - pos < 1) return kErrRead;
+    if (k >= jb.s) {
+      const int32_t o = jb.scatter ? 0 : k * jb.neblock;  // a plane has the window to itself
+      const int rc = decode_stream<Z, STAGE>(jb.fmt, jb.src + pos, cs, jb.srcsize - pos, win + o, wbytes - o,
+                                             jb.neblock, zw);
+      if (rc < 0) return rc;
+    }
+    pos += cs > 0 ? cs : (cs < 0 ? 1 : 0);
+  }
+  __syncwarp();
+  if (jb.scatter) {  // unshuffle of one plane: raw[i * ts + s] = plane[i] (shuffle-generic.h:62-81)
+    uint8_t* o = jb.raw + jb.s;
+    for (int i = lane; i < jb.neblock; i += 32) o[(size_t)i * jb.ns] = win[i];
+  } else if (win != jb.raw) {
+    filter_backward(jb.filter, jb.typesize, jb.bsize, win, jb.raw, jb.version, lane, 32);
+  }
+  return 0;
+}
+
 template <bool Z>
-__global__ void __launch_bounds__(kCtaThreads) k_decode(DecodeArgs a) {
-  uint8_t* smem = dyn_smem();
-  uint8_t* win_s = smem;                                       // [win_bytes]
-  DecodeShared* sh = (DecodeShared*)(smem + a.win_bytes);      // win_bytes is a multiple of 16
-  ZWork* zwork = (ZWork*)(smem + a.win_bytes + 256);           // [kCtaWarps] when Z
-  const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
-  const int nthr = (int)blockDim.x, nwarps = nthr >> 5;  // 32 x (streams per block, at most kCtaWarps)
+__global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
+  const int warp = warp_id(), lane = lane_id();
+  uint8_t* win_s = dyn_smem() + (size_t)warp * (size_t)a.wstride;
+  ZWork* zw = Z ? (ZWork*)(win_s + a.wcap) : nullptr;
+  const int gwarp = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp;
   int hint = 0;
   for (;;) {
-    __syncthreads();  // previous item fully retired (window + sh reusable)
-    if (tid == 0) {
-      int item = atomicAdd(&a.ctl->ticket, 1);
-      int c = -1;
-      if (item < a.ctl->total_items) c = find_chunk(a.base, a.n, item, hint);
-      sh->item = item;
-      sh->chunk = c;
-      sh->err = 0;
-    }
-    __syncthreads();
-    const int c = sh->chunk;
-    if (c < 0) break;
+    int item = 0;
+    if (lane == 0) item = atomicAdd(&a.ctl->ticket, 1);
+    item = __shfl_sync(kFull, item, 0);
+    if (item >= a.ctl->total_items) break;
+    const int c = find_chunk(a.base, a.n, item, hint);
     hint = c;
-    const int item = sh->item;
     const DInfo d = a.info[c];
     const DChunk ch = a.chunks[c];
-    const int j = item - d.item_base;
-    const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
-    const int32_t bsize = is_left ? d.leftover : d.blocksize;
-    uint8_t* raw = ch.dst + (size_t)j * d.blocksize;
+    const int it = item - d.item_base;
 
-    if (d.special) {  // blosc2.c:1694-1718
-      if (d.special == 1 || d.special == 4) {
-        fill_bytes(raw, 0, bsize, tid, nthr);  // 4 = uninitialised: any content is legal, zeros are stable
+    if (d.special || d.memcpyed) {  // one item per block
+      const int j = it;
+      const int32_t bsize = (j == d.nblocks - 1 && d.leftover > 0) ? d.leftover : d.blocksize;
+      uint8_t* raw = ch.dst + (size_t)j * d.blocksize;
+      if (d.memcpyed) {
+        copy_bytes(raw, ch.src + d.hdr + (size_t)j * d.blocksize, bsize, lane, 32);
+      } else if (d.special == 1 || d.special == 4) {  // blosc2.c:1694-1718
+        fill_bytes(raw, 0, bsize, lane, 32);  // 4 = uninitialised: any content is legal, zeros are stable
       } else if (d.special == 2) {
         if (d.typesize == 4) {
-          for (int i = tid; i < bsize / 4; i += nthr) st_le32(raw + 4 * i, 0x7fc00000);
+          for (int i = lane; i < bsize / 4; i += 32) st_le32(raw + 4 * i, 0x7fc00000);
         } else {
-          for (int i = tid; i < bsize / 8; i += nthr) { st_le32(raw + 8 * i, 0); st_le32(raw + 8 * i + 4, 0x7ff80000); }
+          for (int i = lane; i < bsize / 8; i += 32) { st_le32(raw + 8 * i, 0); st_le32(raw + 8 * i + 4, 0x7ff80000); }
         }
       } else {
         const size_t o = (size_t)j * d.blocksize;
-        for (int i = tid; i < bsize; i += nthr) raw[i] = ch.src[kHdrExt + (o + i) % d.vts];
+        for (int i = lane; i < bsize; i += 32) raw[i] = ch.src[kHdrExt + (o + i) % d.vts];
       }
-      continue;
-    }
-    if (d.memcpyed) {
-      copy_bytes(raw, ch.src + d.hdr + (size_t)j * d.blocksize, bsize, tid, nthr);
       continue;
     }
 
-    const int nstreams = (!d.dont_split && !is_left) ? d.typesize : 1;
-    const int32_t neblock = bsize / nstreams;
+    // item -> (block j, streams [s, s_end) of ns)
+    const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
+    const int per_block = d.serial ? 1 : d.nstreams;
+    int j, s, ns;
+    if (it < full * per_block) { j = it / per_block; s = it - j * per_block; ns = d.nstreams; }
+    else { j = full; s = 0; ns = 1; }
+    const int s_end = d.serial ? ns : s + 1;
+    const int32_t bsize = j < full ? d.blocksize : d.leftover;
+    const int32_t neblock = bsize / ns;
+    uint8_t* raw = ch.dst + (size_t)j * d.blocksize;
     const int32_t srcsize = min(ch.src_bytes, d.cbytes);
-    // stream directory (serial: each csize tells where the next stream starts)
-    if (tid == 0) {
-      int err = 0;
-      const int32_t off = ld_le32(ch.src + d.hdr + 4 * j);
-      if (off <= 0 || off >= srcsize) err = kErrData;
-      if (neblock == 0) err = kErrWrite;
-      if (nstreams > kMaxStreams) err = kErrData;
-      int32_t pos = off;
-      for (int s = 0; s < nstreams && !err; s++) {
-        if (srcsize - pos < 4) { err = kErrRead; break; }
-        const int32_t cs = ld_le32(ch.src + pos);
-        pos += 4;
-        sh->spos[s] = pos;
-        sh->scsize[s] = cs;
-        if (cs > 0) {
-          if (srcsize - pos < cs) { err = kErrRead; break; }
-          pos += cs;
-        } else if (cs < 0) {
-          if (srcsize - pos < 1) { err = kErrRead; break; }
-          pos += 1;
-        }
-      }
-      sh->err = err;
-    }
-    __syncthreads();
-    if (sh->err) {
-      if (tid == 0) set_status(a.res, c, sh->err);
-      continue;
-    }
-    const bool direct = d.filter == kFilterNone;
-    uint8_t* win = direct ? raw
-                          : (bsize <= a.win_bytes ? win_s : a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride);
-    for (int s = warp; s < nstreams; s += nwarps) {
-      const int32_t pos = sh->spos[s];
-      int rc = decode_stream<Z>(d.fmt, ch.src + pos, sh->scsize[s], srcsize - pos, win + (size_t)s * neblock,
-                                neblock, Z ? zwork + warp : nullptr);
-      if (rc < 0 && lane == 0) atomicCAS(&sh->err, 0, rc);
-    }
-    __syncthreads();
-    if (sh->err) {
-      if (tid == 0) set_status(a.res, c, sh->err);
-      continue;
-    }
-    if (!direct) filter_backward(d.filter, d.typesize, bsize, win, raw, d.version, tid, nthr);
+    const bool scatter = ns > 1 && !d.serial;                 // byte plane s of a split shuffled block
+    const bool direct = !scatter && d.filter == kFilterNone;  // no filter: the window is only a staging area
+    const int32_t need = decode_window_bytes(scatter ? neblock : bsize);
+    // Three window kinds, three instantiations: the shared-memory one must be its own code path so that every access
+    // of the byte-serial decoder compiles to LDS / STS instead of generic loads and stores.
+    StreamJob jb;
+    jb.src = ch.src; jb.raw = raw; jb.srcsize = srcsize; jb.first = ld_le32(ch.src + d.hdr + 4 * j);
+    jb.s = s; jb.s_end = s_end; jb.ns = ns; jb.neblock = neblock; jb.bsize = bsize; jb.scatter = scatter;
+    jb.fmt = d.fmt; jb.filter = d.filter; jb.typesize = d.typesize; jb.version = d.version;
+    int err;
+    if (need <= a.wcap) err = decode_streams<Z, true, true>(jb, win_s, a.wcap, zw);
+    else if (direct) err = decode_streams<Z, false, false>(jb, raw, bsize, zw);
+    else err = decode_streams<Z, true, false>(jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw);
+    if (err && lane == 0) set_status(a.res, c, err);
+    __syncwarp();  // the window is free for the next item
   }
 }
 

@@ -29,62 +29,88 @@ __device__ __forceinline__ bool lz4_varlen(const uint8_t* in, int n, int& pos, i
   }
 }
 
+// Literal run of a sequence: out[op .. op+lit) = in[pos .. pos+lit).  When the stream is decoded in place (the
+// compressed bytes sit further up in the very window that is being written, see k_decode) the two ranges may overlap
+// with the destination below the source; then every 32-byte step loads before it stores.
+template <bool INPLACE>
+__device__ __forceinline__ void lz_literal_copy(uint8_t* out, int op, const uint8_t* in, int pos, int lit, int delta,
+                                                int lane) {
+  if (!INPLACE || delta >= lit) {
+    if (lit <= 32) { if (lane < lit) out[op + lane] = in[pos + lane]; }
+    else if (lit < 128) for (int i = lane; i < lit; i += 32) out[op + i] = in[pos + i];
+    else copy_bytes(out + op, in + pos, lit, lane, 32);
+  } else {
+    for (int i = 0; i < lit; i += 32) {
+      uint8_t v = 0;
+      if (i + lane < lit) v = in[pos + i + lane];
+      __syncwarp();
+      if (i + lane < lit) out[op + i + lane] = v;
+    }
+  }
+}
+
 // Decodes in[0..n) into out[0..cap).  Returns the decoded size (must equal cap for blosc) or -1.
 // All 32 lanes must call with identical arguments; `out` may be shared or global memory.
-__device__ __forceinline__ int lz4_decode_warp(const uint8_t* in, int n, uint8_t* out, int cap) {
+// INPLACE: in == out + a (the input is staged at the top of the output window).  Output never passes unread input
+// in a stream that compresses; when a sequence would, -2 is returned and the caller decodes from the original bytes.
+// Header bytes are fetched with warp-uniform loads (one broadcast each), and the next token is fetched before the
+// copies of the current sequence are issued, so its latency overlaps them.
+template <bool INPLACE>
+__device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8_t* out, int cap, int a) {
   const int lane = lane_id();
-  int ip = 0, op = 0;
   if (n <= 0 || cap <= 0) return -1;
+  int ip = 0, op = 0;
+  uint32_t tok = in[0];
+  uint32_t nxt = n > 1 ? in[1] : 0u;
   for (;;) {
     if (ip >= n) return -1;
-    // 32-byte register window over the input: lane l holds in[ip + l]
-    const uint32_t wb = (ip + lane < n) ? in[ip + lane] : 0u;
-    const uint32_t token = __shfl_sync(kFull, wb, 0);
-    int lit = (int)(token >> 4);
+    int lit = (int)(tok >> 4);
     int pos = ip + 1;
     if (lit == 15) {
       if (pos >= n - 15) return -1;
-      if (!lz4_varlen(in, n, pos, n - 15, lit, lane)) return -1;
+      if (nxt != 255u) { lit += (int)nxt; pos++; }
+      else if (!lz4_varlen(in, n, pos, n - 15, lit, lane)) return -1;
     }
-    const int hdr = pos - ip;
     const int cpy = op + lit;
+    const int delta = a + pos - op;
     if (cpy > cap - 12 || pos + lit > n - 8) {
       // must be the last sequence: literals only, consuming the input exactly (lz4.c:2279-2320)
       if (pos + lit != n || cpy > cap) return -1;
-      if (hdr + lit <= 32) {
-        if (lane >= hdr && lane < hdr + lit) out[op + lane - hdr] = (uint8_t)wb;
-      } else {
-        copy_bytes(out + op, in + pos, lit, lane, 32);
-      }
+      lz_literal_copy<INPLACE>(out, op, in, pos, lit, delta, lane);
       op = cpy;
       break;
     }
-    uint32_t offset;
-    if (hdr + lit + 2 <= 32) {
-      if (lane >= hdr && lane < hdr + lit) out[op + lane - hdr] = (uint8_t)wb;
-      offset = __shfl_sync(kFull, wb, hdr + lit) | (__shfl_sync(kFull, wb, hdr + lit + 1) << 8);
-    } else {
-      if (lit >= 64) copy_bytes(out + op, in + pos, lit, lane, 32);
-      else for (int i = lane; i < lit; i += 32) out[op + i] = in[pos + i];
-      offset = (uint32_t)in[pos + lit] | ((uint32_t)in[pos + lit + 1] << 8);
-    }
-    ip = pos + lit + 2;
-    op = cpy;
-    int ml = (int)(token & 15u);
+    const int opos = pos + lit;
+    const uint32_t offset = (uint32_t)in[opos] | ((uint32_t)in[opos + 1] << 8);
+    int ipn = opos + 2;                       // <= n - 6
+    uint32_t t0 = in[ipn], t1 = in[ipn + 1];  // next token (or the match-length extension)
+    lz_literal_copy<INPLACE>(out, op, in, pos, lit, delta, lane);
+    int ml = (int)(tok & 15u);
     if (ml == 15) {
-      if (!lz4_varlen(in, n, ip, n - 4, ml, lane)) return -1;
+      if (t0 != 255u) { ml += (int)t0; ipn++; }
+      else if (!lz4_varlen(in, n, ipn, n - 4, ml, lane)) return -1;
+      t0 = ipn < n ? in[ipn] : 0u;
+      t1 = ipn + 1 < n ? in[ipn + 1] : 0u;
     }
     ml += 4;
-    const int match = op - (int)offset;
-    if (match < 0 || offset == 0) return -1;
-    const int mend = op + ml;
+    if ((int)offset > cpy || offset == 0) return -1;
+    const int mend = cpy + ml;
     if (mend > cap - 5) return -1;  // lz4.c:2419-2423: the last 5 bytes are always literals
+    if (INPLACE && mend > a + ipn) return -2;
     __syncwarp();                   // literals (and every earlier match) visible before the match is read
-    lz_match_copy(out, op, (int)offset, ml, lane);
+    if (ml <= 32 && (int)offset >= ml) { if (lane < ml) out[cpy + lane] = out[cpy - (int)offset + lane]; }
+    else lz_match_copy(out, cpy, (int)offset, ml, lane);
     op = mend;
+    ip = ipn;
+    tok = t0;
+    nxt = t1;
   }
   __syncwarp();
   return op;
+}
+
+__device__ __forceinline__ int lz4_decode_warp(const uint8_t* in, int n, uint8_t* out, int cap) {
+  return lz4_decode_warp_t<false>(in, n, out, cap, 0);
 }
 
 // ---- helpers shared with the encoder (b2g_lzenc.cuh) ---------------------------------------------------------------

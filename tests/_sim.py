@@ -33,7 +33,7 @@ def _ptrs(arrs):
     return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
 
 
-def decompress_batch(chunks, caps=None, win_bytes=32768, max_block=None, grid=2, zstd_ok=True, srcsizes=None):
+def decompress_batch(chunks, caps=None, win_bytes=33280, max_block=None, grid=2, zstd_ok=True, srcsizes=None):
     """-> list of (status, bytes)."""
     n = len(chunks)
     chunks = [np.ascontiguousarray(c) for c in chunks]

@@ -12,8 +12,8 @@ static size_t au(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 extern "C" {
 
-// Decompress a batch.  grid = number of simulated persistent CTAs; win_bytes = shared window (blocks above it use
-// the slab path).  out[i] = nbytes or 0, status[i] = 0 or error.
+// Decompress a batch.  grid = number of simulated persistent CTAs; win_bytes = shared window of one warp (streams
+// that need more use the slab path).  out[i] = nbytes or 0, status[i] = 0 or error.
 int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes, void* const* dsts,
                          const int32_t* caps, int32_t* out, int32_t* status, int win_bytes, int max_block, int grid,
                          int zstd_ok) {
@@ -34,17 +34,18 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   pa.chunks = ch.data(); pa.info = info.data(); pa.res = res.data(); pa.base = base.data(); pa.ctl = ctl;
   pa.n = n; pa.max_block = max_block; pa.zstd_ok = zstd_ok;
   cusim::launch(dim3(1), dim3(1024), 2 * 1024 * sizeof(int32_t), [&] { k_plan_decode(pa); });
-  const size_t stride = au((size_t)max_block + 512, 256);
-  std::vector<uint8_t> slab(stride * grid + 256);
+  const int warps = 2;  // independent workers per simulated CTA
+  const size_t stride = au((size_t)decode_window_bytes(max_block) + 256, 256);
+  std::vector<uint8_t> slab(stride * grid * warps + 256);
   DecodeArgs da;
   da.chunks = ch.data(); da.info = info.data(); da.res = res.data(); da.base = base.data(); da.ctl = &ctl[0];
-  da.n = n; da.win_bytes = win_bytes; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
-  cusim::launch(dim3(grid), dim3(kCtaThreads), (size_t)win_bytes + 256, [&] { k_decode<false>(da); });
+  da.n = n; da.wcap = win_bytes; da.wstride = win_bytes; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
+  cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<false>(da); });
   if (zstd_ok) {
     da.base = base.data() + (n + 1);
     da.ctl = &ctl[1];
-    cusim::launch(dim3(grid), dim3(kCtaThreads), (size_t)win_bytes + 256 + sizeof(ZWork) * kCtaWarps,
-                  [&] { k_decode<true>(da); });
+    da.wstride = win_bytes + (int)au(sizeof(ZWork), 16);
+    cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<true>(da); });
   }
   for (int i = 0; i < n; i++) {
     status[i] = res[i].status;
