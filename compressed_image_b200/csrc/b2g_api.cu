@@ -66,7 +66,6 @@ struct HostBuf {  // pinned
 };
 
 constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
-constexpr size_t kCompressSharedBytes = 256;
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -101,12 +100,7 @@ struct b2g_ctx {
   int blocksize = 32768;   // context blocksize (compress) / largest block the decode path is sized for (slab, plan)
   int stream_hint = 32768; // stream size the decode windows are sized for on the device-resident path
   int win_bytes = 32768;   // shared-memory window (standalone filters)
-  int cwin_bytes = 32768;  // shared-memory window (compress)
-  size_t comp_smem = 0;
-  int comp_grid = 0;
-  int comp_threads = kCtaThreads;  // 32 x streams per block (<= kCtaWarps warps)
-  int htab_bytes = 4096;           // per-warp encoder hash table
-  int max_grid_warps = 0;          // most decode warps any launch of this context has used (sizes the slab)
+  int max_grid_warps = 0;  // most worker warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
   // device + pinned work buffers
   DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
@@ -132,22 +126,34 @@ int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
 
 size_t slab_stride(const b2g_ctx* c);
 
-// Compress geometry: fixed at creation from the context's own parameters.
-int set_compress_geometry(b2g_ctx* c) {
-  const int bs = std::max(c->p.blocksize, 1);
-  c->cwin_bytes = std::max((int)align_up((size_t)bs, 16), 1024);
-  // CTA width: one warp per stream of a block
-  const int cstreams = plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, bs);
-  const int cwarps = plan_cta_warps(cstreams);
-  c->comp_threads = 32 * cwarps;
-  c->htab_bytes = plan_htab_bytes(bs / cstreams);
-  c->comp_smem = (size_t)c->cwin_bytes + (size_t)cwarps * (size_t)(c->htab_bytes + kEncWorkBytes) + kCompressSharedBytes;
-  c->comp_grid = 0;
-  if (c->comp_smem > 227 * 1024) return 0;  // compress calls on this context report B2G_ERR_BLOCKSIZE
-  if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, c->comp_smem)) return rc;
+// Compress launch geometry for a batch whose largest stream is `max_stream` bytes: like decode, every warp is an
+// independent worker (window + hash table + encoder work area), so the CTA shape only decides how many fit an SM.
+constexpr int kMaxEncoderStream = 192 * 1024;  // window + 8 KiB table + work area must fit 227 KiB
+struct CompGeom {
+  int win, htab, warps, grid;
+  size_t smem;
+};
+int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
+  g.win = std::max((int)align_up((size_t)std::max(max_stream, 1), 16), 1024);
+  g.htab = plan_htab_bytes(max_stream);
+  const size_t per = (size_t)g.win + (size_t)g.htab + kEncWorkBytes;
+  int best = 0;
+  g.warps = 1;
+  for (int w : {1, 2, 3, 4, 6, 8}) {
+    const size_t cta = (size_t)w * per;
+    if (cta > 227 * 1024) break;
+    int n = (int)((228 * 1024) / (cta + 1024));
+    n = std::min(n, std::min(32, 64 / w));
+    if (w * n >= best) { best = w * n; g.warps = w; }
+  }
+  g.smem = (size_t)g.warps * per;
+  if (g.smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
+  if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, g.smem)) return rc;
   int occ = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, c->comp_threads, c->comp_smem));
-  c->comp_grid = c->sms * std::max(occ, 1);
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, 32 * g.warps, g.smem));
+  g.grid = c->sms * std::max(occ, 1);
+  const size_t max_warps = std::max((size_t)c->sms, ((size_t)1 << 30) / slab_stride(c));
+  g.grid = (int)std::min<size_t>((size_t)g.grid, std::max<size_t>(max_warps / g.warps, 1));
   return 0;
 }
 
@@ -207,7 +213,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   if (want_zstd) if (int rc = decode_geometry(c, stream_bytes, true, gz)) return rc;
   // slab: windows for streams larger than the shared-memory window, one per warp of the grid
   c->max_grid_warps = std::max(c->max_grid_warps, std::max(g.grid * g.warps, gz.grid * gz.warps));
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, c->max_grid_warps))) return rc;
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)c->max_grid_warps)) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = L.d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
@@ -257,27 +263,31 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
 }
 
 int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(c->comp_grid, c->max_grid_warps))) return rc;
   const b2g_params& p = c->p;
   if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
   if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
   if (p.clevel > 9) return B2G_ERR_CODEC_PARAM;
-  if (c->comp_smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
   if (int rc = L.h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
   if (int rc = L.h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
   CInfo* ci = (CInfo*)L.h_cinfo.p;
   int32_t* base = (int32_t*)L.h_base.p;
   int64_t items = 0;
+  int max_stream = 1;
   CParams cp;
   cp.codec = p.codec; cp.clevel = p.clevel; cp.typesize = p.typesize; cp.filter = p.filter;
   for (int i = 0; i < n; i++) {
-    const int nit = plan_compress_chunk(ci[i], cp, c->p.blocksize, nbytes[i], h_desc[i].dst_cap, c->cwin_bytes);
+    const int nit = plan_compress_chunk(ci[i], cp, c->p.blocksize, nbytes[i], h_desc[i].dst_cap, kMaxEncoderStream);
+    if (ci[i].status == 0) max_stream = std::max(max_stream, ci[i].max_stream);
     ci[i].item_base = (int32_t)items;
     base[i] = (int32_t)items;
     items += nit;
     if (items > INT32_MAX) return B2G_ERR_MAX_BUFSIZE;
   }
   base[n] = (int32_t)items;
+  CompGeom g;
+  if (int rc = compress_geometry(c, max_stream, g)) return rc;
+  c->max_grid_warps = std::max(c->max_grid_warps, g.grid * g.warps);
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)c->max_grid_warps)) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = L.d_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
   if (int rc = L.d_state.ensure(sizeof(CState) * (size_t)n)) return rc;
@@ -305,11 +315,11 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.slab = (uint8_t*)L.d_slab.p;
   ca.slab_stride = (int64_t)slab_stride(c);
   ca.n = n;
-  ca.win_bytes = c->cwin_bytes;
-  ca.htab_bytes = c->htab_bytes;
+  ca.win_bytes = g.win;
+  ca.htab_bytes = g.htab;
   ca.p = cp;
-  const int cgrid = (int)std::min<int64_t>(c->comp_grid, items);
-  k_compress<<<cgrid, c->comp_threads, c->comp_smem, s>>>(ca);
+  const int cgrid = (int)std::min<int64_t>(g.grid, (items + g.warps - 1) / g.warps);
+  k_compress<<<cgrid, 32 * g.warps, g.smem, s>>>(ca);
   c->launches++;
   FinalizeArgs fa;
   fa.chunks = ca.chunks;
@@ -375,7 +385,6 @@ b2g_ctx* b2g_create(const b2g_params* params) {
     if (ok) ok = !cuda_fail(cudaEventCreateWithFlags(&L.res_ready, cudaEventDisableTiming), "cudaEventCreate");
   }
   c->stream_hint = c->p.blocksize / plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, c->p.blocksize);
-  if (ok) ok = set_compress_geometry(c) == 0;
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;
   if (!ok) { b2g_destroy(c); return nullptr; }
   return c;

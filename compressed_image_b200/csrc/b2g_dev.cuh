@@ -61,6 +61,9 @@ struct CInfo {
   int32_t memcpyed;      // clevel 0 or nbytes < 32: stored chunk
   int32_t dont_split;
   int32_t status;        // host-side validation result (0 = ok)
+  int32_t nitems;        // stream work items of the chunk (0 for stored chunks); the chunk occupies
+                         // max(nitems, nblocks, 1) item numbers so that k_finalize has one per block to copy
+  int32_t max_stream;    // largest stream of the chunk in bytes (sizes the encoder window)
 };
 
 // Per-chunk running state of a compress batch (device, zero-initialised per batch).

@@ -7,10 +7,11 @@
 //                   (lz4 / blosclz / zstd / stored / run / zero: blosc_d, blosc2.c:1568-1937), then the fused un-filter:
 //                   a byte plane is scattered into the raw block, whole-block streams are un(bit)shuffled
 //                   (pipeline_backward, blosc2.c:1336-1461).  <Z = true> adds the zstd work area; zstd chunks only.
-//   k_compress      persistent CTAs, ticket order: fused filter into the shared window (pipeline_forward,
-//                   blosc2.c:940-1050), one warp per stream (run detection blosc2.c:1054-1076, lz4 / blosclz, raw
-//                   fallback: blosc_c, blosc2.c:1080-1332) into an L2-resident per-CTA slab, decoupled look-back over
-//                   the chunk's blocks for the output offset, compaction into the chunk with bstarts.
+//   k_compress      persistent independent warps, stream items in ticket order: fused filter into the warp's shared
+//                   window (pipeline_forward, blosc2.c:940-1050; a byte plane is gathered straight from the raw block),
+//                   run detection (blosc2.c:1054-1076), lz4 / blosclz, raw fallback (blosc_c, blosc2.c:1080-1332) into
+//                   an L2-resident per-warp slab, decoupled look-back over the chunk's streams for the output offset,
+//                   compaction into the chunk with bstarts.
 //   k_finalize      chunk headers, SPECIAL_ZERO and memcpyed fallbacks (blosc2.c:2393-2529).
 //   k_filter        standalone filters (K1-K4).
 #pragma once
@@ -281,7 +282,16 @@ __device__ __forceinline__ int decode_streams(const StreamJob& jb, uint8_t* win,
   __syncwarp();
   if (jb.scatter) {  // unshuffle of one plane: raw[i * ts + s] = plane[i] (shuffle-generic.h:62-81)
     uint8_t* o = jb.raw + jb.s;
-    for (int i = lane; i < jb.neblock; i += 32) o[(size_t)i * jb.ns] = win[i];
+    const int ns = jb.ns;
+    int i = lane;
+    for (; i + 7 * 32 < jb.neblock; i += 8 * 32) {  // 8 loads in flight, then 8 stores
+      uint8_t v[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) v[u] = win[i + 32 * u];
+#pragma unroll
+      for (int u = 0; u < 8; u++) o[(size_t)(i + 32 * u) * ns] = v[u];
+    }
+    for (; i < jb.neblock; i += 32) o[(size_t)i * ns] = win[i];
   } else if (win != jb.raw) {
     filter_backward(jb.filter, jb.typesize, jb.bsize, win, jb.raw, jb.version, lane, 32);
   }
@@ -364,21 +374,13 @@ struct CompressArgs {
   const int32_t* base;           // [n + 1]
   BatchCtl* ctl;
   unsigned long long* desc;      // [total_items] look-back descriptors, zeroed per batch
-  uint8_t* slab;                 // per-CTA scratch for compressed streams
+  uint8_t* slab;                 // per-warp scratch for the compressed stream
   int64_t slab_stride;
   int32_t n;
-  int32_t win_bytes;
+  int32_t win_bytes;             // shared-memory window of one warp: the largest stream of the batch
   int32_t htab_bytes;            // per-warp hash table bytes (a power of two); each warp's work area is
                                  // htab_bytes + kEncWorkBytes, see enc_work()
   CParams p;
-};
-
-struct CompressShared {
-  int32_t item, chunk;
-  int32_t psize[kMaxStreams];   // payload bytes of each stream (0 or 1 for zero / run streams)
-  int32_t csize[kMaxStreams];   // csize field as written
-  int32_t raw[kMaxStreams];     // payload is the raw window (stored stream)
-  int32_t offset;               // byte offset of this block inside the chunk
 };
 
 constexpr unsigned long long kDescAggregate = 1ull << 62, kDescInclusive = 2ull << 62, kDescMask = (1ull << 62) - 1;
@@ -402,122 +404,142 @@ __device__ __forceinline__ bool warp_is_run(const uint8_t* in, int n, int lane) 
   return __all_sync(kFull, same);
 }
 
-__global__ void __launch_bounds__(kCtaThreads) k_compress(CompressArgs a) {
-  // blockDim.x = 32 x (streams per block, at most kCtaWarps): every warp of the CTA owns a stream
-  uint8_t* smem = dyn_smem();
-  uint8_t* win = smem;                                            // [win_bytes] filtered block
-  const int tid = (int)threadIdx.x, warp = warp_id(), lane = lane_id();
-  const int nthr = (int)blockDim.x, nwarps = nthr >> 5;
-  const int work_bytes = a.htab_bytes + kEncWorkBytes;
-  uint8_t* work = smem + a.win_bytes + (size_t)warp * work_bytes;
-  CompressShared* sh = (CompressShared*)(smem + a.win_bytes + (size_t)nwarps * work_bytes);
-  uint8_t* slab = a.slab + (size_t)blockIdx.x * (size_t)a.slab_stride;
+// Byte plane s of a raw block into the window: win[i] = raw[i * ts + s] (the forward shuffle restricted to one plane,
+// shuffle-generic.h:34-53).  Every plane's warp streams the whole raw block with 128-bit loads (the block is read from
+// HBM once; the other planes' warps find it in L2).
+__device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const uint8_t* raw, uint8_t* win, int lane) {
+  const int bytes = neblock * ts;
+  if ((ts == 2 || ts == 4 || ts == 8 || ts == 16) && (((uintptr_t)raw | (uintptr_t)win) & 15) == 0 && (bytes & 15) == 0) {
+    const uint4* r4 = (const uint4*)raw;
+    const int groups = bytes >> 4;
+    if (ts == 2) {
+      const uint32_t sel = s ? 0x7531u : 0x6420u;
+      for (int g = lane; g < groups; g += 32) {
+        const uint4 v = r4[g];
+        *(uint2*)(win + 8 * g) = make_uint2(__byte_perm(v.x, v.y, sel), __byte_perm(v.z, v.w, sel));
+      }
+    } else if (ts == 4) {
+      const uint32_t sel = (uint32_t)s | ((uint32_t)(4 + s) << 4);
+      for (int g = lane; g < groups; g += 32) {
+        const uint4 v = r4[g];
+        const uint32_t lo = __byte_perm(v.x, v.y, sel), hi = __byte_perm(v.z, v.w, sel);
+        *(uint32_t*)(win + 4 * g) = __byte_perm(lo, hi, 0x5410);
+      }
+    } else if (ts == 8) {
+      const uint32_t sel = (uint32_t)(s & 3) | ((uint32_t)(4 + (s & 3)) << 4);
+      for (int g = lane; g < groups; g += 32) {
+        const uint4 v = r4[g];
+        *(uint16_t*)(win + 2 * g) = (uint16_t)(s < 4 ? __byte_perm(v.x, v.z, sel) : __byte_perm(v.y, v.w, sel));
+      }
+    } else {
+      for (int g = lane; g < groups; g += 32) {
+        const uint4 v = r4[g];
+        const uint32_t w = s < 4 ? v.x : (s < 8 ? v.y : (s < 12 ? v.z : v.w));
+        win[g] = (uint8_t)(w >> (8 * (s & 3)));
+      }
+    }
+    return;
+  }
+  const uint8_t* r = raw + s;
+  for (int i = lane; i < neblock; i += 32) win[i] = r[(size_t)i * ts];
+}
+
+// Work item = one stream (a byte plane of a split block, or a whole unsplit / leftover block), one independent warp per
+// item: gather + filter into the warp's window, run detection, encode into the warp's slab, decoupled look-back over
+// the chunk's earlier streams for the output offset, compaction.  No warp ever waits at a CTA barrier.
+__global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
+  const int warp = warp_id(), lane = lane_id();
+  const int wstride = a.win_bytes + a.htab_bytes + kEncWorkBytes;
+  uint8_t* win = dyn_smem() + (size_t)warp * (size_t)wstride;   // [win_bytes] the filtered stream
+  uint8_t* work = win + a.win_bytes;
+  const int gwarp = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp;
+  uint8_t* out = a.slab + (size_t)gwarp * (size_t)a.slab_stride;
+  const int ts = a.p.typesize;
   int hint = 0;
   for (;;) {
-    __syncthreads();
-    if (tid == 0) {
-      int item = atomicAdd(&a.ctl->ticket, 1);
-      int c = -1;
-      if (item < a.ctl->total_items) c = find_chunk(a.base, a.n, item, hint);
-      sh->item = item;
-      sh->chunk = c;
-    }
-    __syncthreads();
-    const int c = sh->chunk;
-    if (c < 0) break;
+    int item = 0;
+    if (lane == 0) item = atomicAdd(&a.ctl->ticket, 1);
+    item = __shfl_sync(kFull, item, 0);
+    if (item >= a.ctl->total_items) break;
+    const int c = find_chunk(a.base, a.n, item, hint);
     hint = c;
-    const int item = sh->item;
     const CInfo d = a.info[c];
-    const int j = item - d.item_base;
-    if (d.status < 0 || d.memcpyed || j >= d.nblocks) continue;  // k_finalize stores these chunks
+    const int it = item - d.item_base;
+    if (d.status < 0 || d.memcpyed || it >= d.nitems) continue;  // k_finalize stores these chunks
     const DChunk ch = a.chunks[c];
-    const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
-    const int32_t bsize = is_left ? d.leftover : d.blocksize;
-    const int ts = a.p.typesize;
-    filter_forward(a.p.filter, ts, bsize, ch.src + (size_t)j * d.blocksize, win, tid, nthr);
-    __syncthreads();
-    const int nstreams = (!d.dont_split && !is_left) ? ts : 1;
-    const int32_t neblock = bsize / nstreams;
-    const int32_t sstride = (neblock + 15) & ~15;  // slab region per stream
-    int hlog = 28 - __clz(neblock);                // floor(log2(neblock)) - 3: table bytes <= neblock / 4
-    const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
-    hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
-    const EncWork ew = enc_work(work, a.htab_bytes, hlog);
-    for (int s = warp; s < nstreams; s += nwarps) {
-      const uint8_t* in = win + (size_t)s * neblock;
-      uint8_t* out = slab + (size_t)s * sstride;
-      int32_t psize, csize, raw = 0;
-      if (warp_is_run(in, neblock, lane)) {
-        const uint8_t v = in[0];
-        csize = -(int32_t)v;
-        psize = v ? 1 : 0;
-        if (lane == 0 && v) out[0] = 0x01;
-      } else {
-        int r = 0;
-        const int cap = neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
-        if (a.p.codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(in, neblock, out, cap, ew);
-        else r = lz_encode_warp<kCodecBlosclz>(in, neblock, out, cap, ew);
-        if (r <= 0 || r >= neblock) { raw = 1; psize = csize = neblock; }
-        else psize = csize = r;
-      }
-      if (lane == 0) { sh->psize[s] = psize; sh->csize[s] = csize; sh->raw[s] = raw; }
+    // item -> (block j, stream s of ns)
+    const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
+    const int nsf = d.dont_split ? 1 : ts;
+    int j, s, ns;
+    if (it < full * nsf) { j = it / nsf; s = it - j * nsf; ns = nsf; }
+    else { j = full; s = 0; ns = 1; }
+    const int32_t bsize = j < full ? d.blocksize : d.leftover;
+    const int32_t neblock = bsize / ns;
+    const uint8_t* raw = ch.src + (size_t)j * d.blocksize;
+    if (ns > 1) gather_plane(ts, s, neblock, raw, win, lane);
+    else filter_forward(a.p.filter, ts, bsize, raw, win, lane, 32);
+    __syncwarp();
+    int32_t psize, csize;
+    bool stored = false;
+    if (warp_is_run(win, neblock, lane)) {
+      const uint8_t v = win[0];
+      csize = -(int32_t)v;
+      psize = v ? 1 : 0;
+      if (lane == 0 && v) out[0] = 0x01;
+    } else {
+      int hlog = 28 - __clz(neblock);                // floor(log2(neblock)) - 3: table bytes <= neblock / 4
+      const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
+      hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
+      const EncWork ew = enc_work(work, a.htab_bytes, hlog);
+      const int cap = neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
+      int r;
+      if (a.p.codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(win, neblock, out, cap, ew);
+      else r = lz_encode_warp<kCodecBlosclz>(win, neblock, out, cap, ew);
+      if (r <= 0 || r >= neblock) { stored = true; psize = csize = neblock; }
+      else psize = csize = r;
     }
-    __syncthreads();
-    // block size + decoupled look-back over the earlier blocks of this chunk (warp 0)
-    if (warp == 0) {
-      int32_t total = 0, nonzero = 0;
-      for (int s = 0; s < nstreams; s++) { total += 4 + sh->psize[s]; nonzero += sh->csize[s] != 0; }
-      const int first = d.item_base;
-      unsigned long long prefix = 0;
-      if (item > first) {
-        if (lane == 0) st_release_u64(&a.desc[item], kDescAggregate | (unsigned long long)total);
-        int look = item - 1;
-        for (;;) {
-          const int idx = look - lane;
-          unsigned long long v = kDescInclusive;  // lanes before the chunk start act as a zero inclusive prefix
-          if (idx >= first) {
-            for (;;) {
-              v = ld_acquire_u64(&a.desc[idx]);
-              if (v >> 62) break;
-              B2G_SPIN_PAUSE();
-            }
+    // decoupled look-back over the earlier streams of this chunk
+    const int32_t total = 4 + psize;
+    const int first = d.item_base;
+    unsigned long long prefix = 0;
+    if (item > first) {
+      if (lane == 0) st_release_u64(&a.desc[item], kDescAggregate | (unsigned long long)total);
+      int look = item - 1;
+      for (;;) {
+        const int idx = look - lane;
+        unsigned long long v = kDescInclusive;  // lanes before the chunk start act as a zero inclusive prefix
+        if (idx >= first) {
+          for (;;) {
+            v = ld_acquire_u64(&a.desc[idx]);
+            if (v >> 62) break;
+            B2G_SPIN_PAUSE();
           }
-          const unsigned inc = __ballot_sync(kFull, (v >> 62) == 2);
-          const int stop = inc ? __ffs((int)inc) - 1 : 31;
-          unsigned long long part = lane <= stop ? (v & kDescMask) : 0ull;
-          for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
-          prefix += part;
-          if (inc) break;
-          look -= 32;
         }
-      }
-      if (lane == 0) {
-        st_release_u64(&a.desc[item], kDescInclusive | (prefix + (unsigned long long)total));
-        const int32_t off = kHdrExt + 4 * d.nblocks + (int32_t)prefix;
-        const int32_t limit = min(ch.dst_cap, d.nbytes + kHdrExt);
-        if (off + total > limit) {
-          atomicExch(&a.state[c].overflow, 1);
-          sh->offset = -1;
-        } else {
-          sh->offset = off;
-          st_le32(ch.dst + kHdrExt + 4 * j, off);
-        }
-        if (nonzero) atomicAdd(&a.state[c].nonzero_streams, nonzero);
-        if (j == d.nblocks - 1) a.state[c].total = kHdrExt + 4 * d.nblocks + (int32_t)prefix + total;
+        const unsigned inc = __ballot_sync(kFull, (v >> 62) == 2);
+        const int stop = inc ? __ffs((int)inc) - 1 : 31;
+        unsigned long long part = lane <= stop ? (v & kDescMask) : 0ull;
+        for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
+        prefix += part;
+        if (inc) break;
+        look -= 32;
       }
     }
-    __syncthreads();
-    int32_t off = sh->offset;
-    if (off < 0) continue;
-    // compaction: [csize][payload] per stream, in order
-    for (int s = 0; s < nstreams; s++) {
-      const int32_t ps = sh->psize[s];
-      uint8_t* o = ch.dst + off;
-      if (tid == 0) st_le32(o, sh->csize[s]);
-      const uint8_t* from = sh->raw[s] ? win + (size_t)s * neblock : slab + (size_t)s * sstride;
-      copy_bytes(o + 4, from, ps, tid, nthr);
-      off += 4 + ps;
+    int32_t off = kHdrExt + 4 * d.nblocks + (int32_t)prefix;
+    if (lane == 0) {
+      st_release_u64(&a.desc[item], kDescInclusive | (prefix + (unsigned long long)total));
+      const int32_t limit = min(ch.dst_cap, d.nbytes + kHdrExt);
+      if (off + total > limit) atomicExch(&a.state[c].overflow, 1);
+      else if (s == 0) st_le32(ch.dst + kHdrExt + 4 * j, off);
+      if (csize != 0) atomicAdd(&a.state[c].nonzero_streams, 1);
+      if (it == d.nitems - 1) a.state[c].total = off + total;
     }
+    if (off + total > min(ch.dst_cap, d.nbytes + kHdrExt)) continue;
+    // compaction: [csize][payload]
+    uint8_t* o = ch.dst + off;
+    if (lane == 0) st_le32(o, csize);
+    __syncwarp();  // the encoder's byte stores to the slab are visible to the whole warp
+    copy_bytes(o + 4, stored ? win : out, psize, lane, 32);
+    __syncwarp();  // window and slab are free for the next item
   }
 }
 

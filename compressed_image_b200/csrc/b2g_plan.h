@@ -25,7 +25,8 @@ inline int plan_blocksize(int user, int typesize, int nbytes) {
   return std::max(bs, 1);
 }
 
-// Fills one CInfo; returns the number of work items the chunk occupies (>= 1 so that every chunk gets a header).
+// Fills one CInfo; returns the number of item numbers the chunk occupies (>= 1 so that every chunk gets a header).
+// win_bytes = largest stream the encoder window can take (<= 0: no limit, the caller sizes the window afterwards).
 inline int plan_compress_chunk(CInfo& d, const CParams& p, int user_blocksize, int32_t nbytes, int32_t dst_cap,
                                int win_bytes) {
   memset(&d, 0, sizeof(d));
@@ -39,9 +40,15 @@ inline int plan_compress_chunk(CInfo& d, const CParams& p, int user_blocksize, i
     if (d.leftover > 0) d.nblocks++;
     d.memcpyed = (p.clevel == 0 || nbytes < kMinBuffer) ? 1 : 0;
     d.dont_split = plan_split_block(p.codec, p.clevel, p.filter, p.typesize, d.blocksize) ? 0 : 1;
-    if (!d.memcpyed && d.blocksize > win_bytes) d.status = kErrBlocksize;  // the encoder window is shared memory
+    if (!d.memcpyed) {
+      const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
+      const int ns = d.dont_split ? 1 : p.typesize;
+      d.nitems = full * ns + (d.leftover > 0 ? 1 : 0);
+      d.max_stream = std::max(full > 0 ? d.blocksize / ns : 0, d.leftover);
+      if (win_bytes > 0 && d.max_stream > win_bytes) d.status = kErrBlocksize;  // the encoder window is shared memory
+    }
   }
-  return std::max(d.nblocks, 1);
+  return std::max(std::max(d.nitems, d.nblocks), 1);
 }
 
 // Streams a block of this geometry is stored as (stune.c:185-210), and the warps a CTA gets for it.

@@ -65,14 +65,15 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   memset(state.data(), 0, sizeof(CState) * n);
   CParams p;
   p.codec = (uint8_t)codec; p.clevel = (uint8_t)clevel; p.typesize = (uint8_t)typesize; p.filter = (uint8_t)filter;
-  win_bytes = (int)au(win_bytes, 16);
   int64_t items = 0;
+  int max_stream = 1;
   for (int i = 0; i < n; i++) {
     ch[i].src = (const uint8_t*)srcs[i];
     ch[i].dst = (uint8_t*)dsts[i];
     ch[i].src_bytes = nbytes[i];
     ch[i].dst_cap = caps[i];
     int nit = plan_compress_chunk(info[i], p, blocksize, nbytes[i], caps[i], win_bytes);
+    if (info[i].status == 0) max_stream = std::max(max_stream, info[i].max_stream);
     info[i].item_base = (int32_t)items;
     base[i] = (int32_t)items;
     items += nit;
@@ -82,18 +83,17 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   memset(ctl, 0, sizeof(ctl));
   ctl[0].total_items = (int32_t)items;
   std::vector<unsigned long long> desc(items + 1, 0ull);
-  const size_t stride = au((size_t)win_bytes + 16 * kMaxStreams + 256, 256);
-  std::vector<uint8_t> slab(stride * grid + 256);
+  const int warps = 2;  // independent workers per simulated CTA
+  const int wwin = std::max((int)au(max_stream, 16), 1024);
+  const size_t stride = au((size_t)wwin + 512, 256);
+  std::vector<uint8_t> slab(stride * grid * warps + 256);
   CompressArgs ca;
   ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
   ca.desc = desc.data(); ca.slab = slab.data(); ca.slab_stride = (int64_t)stride; ca.n = n;
-  const int bs = plan_blocksize(blocksize, typesize, 1 << 30);
-  const int nstreams = plan_nstreams(codec, clevel, filter, typesize, bs);
-  const int nwarps = plan_cta_warps(nstreams);
-  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(bs / nstreams);
-  ca.win_bytes = win_bytes; ca.htab_bytes = htab_bytes; ca.p = p;
-  const size_t smem = (size_t)win_bytes + (size_t)nwarps * (htab_bytes + kEncWorkBytes) + 256;
-  cusim::launch(dim3(grid), dim3(32 * nwarps), smem, [&] { k_compress(ca); });
+  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream);
+  ca.win_bytes = wwin; ca.htab_bytes = htab_bytes; ca.p = p;
+  const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + kEncWorkBytes);
+  cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] { k_compress(ca); });
   FinalizeArgs fa;
   fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.res = res.data(); fa.base = base.data();
   fa.n = n; fa.total_items = (int32_t)items; fa.p = p;
