@@ -79,10 +79,10 @@ struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_desc, d_slab;
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
   void release() {
-    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_desc, &d_slab}) b->release();
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab}) b->release();
     for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     if (res_ready) cudaEventDestroy(res_ready);
@@ -113,7 +113,7 @@ struct b2g_ctx {
 namespace {
 
 std::mutex g_attr_mutex;
-size_t g_smem_limit[64][4];  // [device][kernel]
+size_t g_smem_limit[64][8];  // [device][kernel]
 
 int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
   std::lock_guard<std::mutex> lock(g_attr_mutex);
@@ -286,22 +286,20 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   base[n] = (int32_t)items;
   CompGeom g;
   if (int rc = compress_geometry(c, max_stream, g)) return rc;
-  c->max_grid_warps = std::max(c->max_grid_warps, g.grid * g.warps);
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)c->max_grid_warps)) return rc;
+  const size_t scratch_stride = (size_t)g.win;  // an encoded stream is kept only when it is smaller than the stream
+  if (int rc = L.d_items.ensure(sizeof(CItem) * (size_t)items)) return rc;
+  if (int rc = L.d_scratch.ensure(scratch_stride * (size_t)items + 256)) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = L.d_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
   if (int rc = L.d_state.ensure(sizeof(CState) * (size_t)n)) return rc;
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
   if (int rc = L.d_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
   if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
-  if (int rc = L.d_desc.ensure(sizeof(unsigned long long) * (size_t)items)) return rc;
   if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
   CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaMemcpyAsync(L.d_cinfo.p, ci, sizeof(CInfo) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaMemcpyAsync(L.d_base.p, base, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
   CU(cudaEventRecord(L.ev[0], s));
-  CU(cudaMemsetAsync(L.d_state.p, 0, sizeof(CState) * (size_t)n, s));
-  CU(cudaMemsetAsync(L.d_desc.p, 0, sizeof(unsigned long long) * (size_t)items, s));
   CU(cudaMemsetAsync(L.d_ctl.p, 0, sizeof(BatchCtl) * 2, s));
   CU(cudaMemcpyAsync(L.d_ctl.p, &base[n], sizeof(int32_t), cudaMemcpyHostToDevice, s));  // ctl[0].total_items
   CU(cudaEventRecord(L.ev[1], s));
@@ -311,9 +309,9 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.state = (CState*)L.d_state.p;
   ca.base = (const int32_t*)L.d_base.p;
   ca.ctl = (BatchCtl*)L.d_ctl.p;
-  ca.desc = (unsigned long long*)L.d_desc.p;
-  ca.slab = (uint8_t*)L.d_slab.p;
-  ca.slab_stride = (int64_t)slab_stride(c);
+  ca.items = (CItem*)L.d_items.p;
+  ca.scratch = (uint8_t*)L.d_scratch.p;
+  ca.scratch_stride = (int64_t)scratch_stride;
   ca.n = n;
   ca.win_bytes = g.win;
   ca.htab_bytes = g.htab;
@@ -321,17 +319,32 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   const int cgrid = (int)std::min<int64_t>(g.grid, (items + g.warps - 1) / g.warps);
   k_compress<<<cgrid, 32 * g.warps, g.smem, s>>>(ca);
   c->launches++;
+  PlaceArgs pl;
+  pl.chunks = ca.chunks;
+  pl.info = ca.info;
+  pl.items = ca.items;
+  pl.state = ca.state;
+  pl.n = n;
+  k_place<<<std::min(n, c->sms * 4), 256, 2 * 256 * sizeof(int32_t), s>>>(pl);
+  c->launches++;
   FinalizeArgs fa;
   fa.chunks = ca.chunks;
   fa.info = ca.info;
   fa.state = ca.state;
+  fa.items = ca.items;
+  fa.scratch = ca.scratch;
+  fa.scratch_stride = ca.scratch_stride;
   fa.res = (DResult*)L.d_res.p;
   fa.base = ca.base;
   fa.n = n;
   fa.total_items = (int32_t)items;
+  fa.win_bytes = g.win;
   fa.p = ca.p;
-  const int fgrid = (int)std::min<int64_t>((int64_t)c->sms * 16, items);
-  k_finalize<<<fgrid, kCtaThreads, 0, s>>>(fa);
+  if (int rc = raise_smem_limit(c->dev, 4, (const void*)k_finalize, (size_t)g.win)) return rc;
+  int focc = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&focc, k_finalize, kCtaThreads, (size_t)g.win));
+  const int fgrid = (int)std::min<int64_t>((int64_t)c->sms * std::max(focc, 1), items);
+  k_finalize<<<fgrid, kCtaThreads, (size_t)g.win, s>>>(fa);
   c->launches++;
   CU(cudaEventRecord(L.ev[2], s));
   CU(cudaGetLastError());

@@ -367,23 +367,42 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
 }
 
 // ---- compress --------------------------------------------------------------------------------------------------------
+// Result of one stream item (k_compress -> k_place -> k_finalize).
+struct CItem {
+  int32_t csize;   // the stream's csize field (0 zero run, < 0 run of a byte value, == neblock stored, else encoded size)
+  int32_t psize;   // payload bytes that follow the csize field
+  int32_t offset;  // k_place: byte offset of the csize field inside the chunk
+  int32_t stored;  // payload = the filtered stream itself (not kept: k_finalize re-filters it from the source)
+};
+
+// item number inside a chunk -> (block j, stream s of ns, block bytes, stream bytes)
+struct StreamGeom { int j, s, ns, bsize, neblock; };
+__device__ __forceinline__ StreamGeom stream_geometry(const CInfo& d, int ts, int it) {
+  StreamGeom g;
+  const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
+  const int nsf = d.dont_split ? 1 : ts;
+  if (it < full * nsf) { g.j = it / nsf; g.s = it - g.j * nsf; g.ns = nsf; }
+  else { g.j = full; g.s = 0; g.ns = 1; }
+  g.bsize = g.j < full ? d.blocksize : d.leftover;
+  g.neblock = g.bsize / g.ns;
+  return g;
+}
+
 struct CompressArgs {
   const DChunk* chunks;          // src = raw elements, dst = chunk out
   const CInfo* info;
   CState* state;
   const int32_t* base;           // [n + 1]
   BatchCtl* ctl;
-  unsigned long long* desc;      // [total_items] look-back descriptors, zeroed per batch
-  uint8_t* slab;                 // per-warp scratch for the compressed stream
-  int64_t slab_stride;
+  CItem* items;                  // [total_items] what each stream item produced
+  uint8_t* scratch;              // [total_items][scratch_stride] the encoded streams, in item order
+  int64_t scratch_stride;
   int32_t n;
   int32_t win_bytes;             // shared-memory window of one warp: the largest stream of the batch
   int32_t htab_bytes;            // per-warp hash table bytes (a power of two); each warp's work area is
                                  // htab_bytes + kEncWorkBytes, see enc_work()
   CParams p;
 };
-
-constexpr unsigned long long kDescAggregate = 1ull << 62, kDescInclusive = 2ull << 62, kDescMask = (1ull << 62) - 1;
 
 // Is in[0..n) one repeated byte?  (get_run, blosc2.c:1054-1076)
 __device__ __forceinline__ bool warp_is_run(const uint8_t* in, int n, int lane) {
@@ -407,32 +426,42 @@ __device__ __forceinline__ bool warp_is_run(const uint8_t* in, int n, int lane) 
 // Byte plane s of a raw block into the window: win[i] = raw[i * ts + s] (the forward shuffle restricted to one plane,
 // shuffle-generic.h:34-53).  Every plane's warp streams the whole raw block with 128-bit loads (the block is read from
 // HBM once; the other planes' warps find it in L2).
-__device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const uint8_t* raw, uint8_t* win, int lane) {
+__device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const uint8_t* raw, uint8_t* win, int lane,
+                                             int nthr) {
   const int bytes = neblock * ts;
   if ((ts == 2 || ts == 4 || ts == 8 || ts == 16) && (((uintptr_t)raw | (uintptr_t)win) & 15) == 0 && (bytes & 15) == 0) {
     const uint4* r4 = (const uint4*)raw;
     const int groups = bytes >> 4;
     if (ts == 2) {
       const uint32_t sel = s ? 0x7531u : 0x6420u;
-      for (int g = lane; g < groups; g += 32) {
+      int g = lane;
+      for (; g + 3 * nthr < groups; g += 4 * nthr) {  // four loads in flight
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) v[u] = r4[g + u * nthr];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          *(uint2*)(win + 8 * (g + u * nthr)) = make_uint2(__byte_perm(v[u].x, v[u].y, sel), __byte_perm(v[u].z, v[u].w, sel));
+      }
+      for (; g < groups; g += nthr) {
         const uint4 v = r4[g];
         *(uint2*)(win + 8 * g) = make_uint2(__byte_perm(v.x, v.y, sel), __byte_perm(v.z, v.w, sel));
       }
     } else if (ts == 4) {
       const uint32_t sel = (uint32_t)s | ((uint32_t)(4 + s) << 4);
-      for (int g = lane; g < groups; g += 32) {
+      for (int g = lane; g < groups; g += nthr) {
         const uint4 v = r4[g];
         const uint32_t lo = __byte_perm(v.x, v.y, sel), hi = __byte_perm(v.z, v.w, sel);
         *(uint32_t*)(win + 4 * g) = __byte_perm(lo, hi, 0x5410);
       }
     } else if (ts == 8) {
       const uint32_t sel = (uint32_t)(s & 3) | ((uint32_t)(4 + (s & 3)) << 4);
-      for (int g = lane; g < groups; g += 32) {
+      for (int g = lane; g < groups; g += nthr) {
         const uint4 v = r4[g];
         *(uint16_t*)(win + 2 * g) = (uint16_t)(s < 4 ? __byte_perm(v.x, v.z, sel) : __byte_perm(v.y, v.w, sel));
       }
     } else {
-      for (int g = lane; g < groups; g += 32) {
+      for (int g = lane; g < groups; g += nthr) {
         const uint4 v = r4[g];
         const uint32_t w = s < 4 ? v.x : (s < 8 ? v.y : (s < 12 ? v.z : v.w));
         win[g] = (uint8_t)(w >> (8 * (s & 3)));
@@ -441,19 +470,18 @@ __device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const u
     return;
   }
   const uint8_t* r = raw + s;
-  for (int i = lane; i < neblock; i += 32) win[i] = r[(size_t)i * ts];
+  for (int i = lane; i < neblock; i += nthr) win[i] = r[(size_t)i * ts];
 }
 
 // Work item = one stream (a byte plane of a split block, or a whole unsplit / leftover block), one independent warp per
-// item: gather + filter into the warp's window, run detection, encode into the warp's slab, decoupled look-back over
-// the chunk's earlier streams for the output offset, compaction.  No warp ever waits at a CTA barrier.
+// item: gather + filter into the warp's window, run detection, encode into the item's scratch slot.  Where the stream
+// lands in the chunk depends on the sizes of all earlier streams, so placement is a separate pass (k_place, k_finalize):
+// no warp ever waits for another one.
 __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
   const int warp = warp_id(), lane = lane_id();
   const int wstride = a.win_bytes + a.htab_bytes + kEncWorkBytes;
   uint8_t* win = dyn_smem() + (size_t)warp * (size_t)wstride;   // [win_bytes] the filtered stream
   uint8_t* work = win + a.win_bytes;
-  const int gwarp = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp;
-  uint8_t* out = a.slab + (size_t)gwarp * (size_t)a.slab_stride;
   const int ts = a.p.typesize;
   int hint = 0;
   for (;;) {
@@ -466,80 +494,83 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
     const CInfo d = a.info[c];
     const int it = item - d.item_base;
     if (d.status < 0 || d.memcpyed || it >= d.nitems) continue;  // k_finalize stores these chunks
-    const DChunk ch = a.chunks[c];
-    // item -> (block j, stream s of ns)
-    const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
-    const int nsf = d.dont_split ? 1 : ts;
-    int j, s, ns;
-    if (it < full * nsf) { j = it / nsf; s = it - j * nsf; ns = nsf; }
-    else { j = full; s = 0; ns = 1; }
-    const int32_t bsize = j < full ? d.blocksize : d.leftover;
-    const int32_t neblock = bsize / ns;
-    const uint8_t* raw = ch.src + (size_t)j * d.blocksize;
-    if (ns > 1) gather_plane(ts, s, neblock, raw, win, lane);
-    else filter_forward(a.p.filter, ts, bsize, raw, win, lane, 32);
+    const StreamGeom g = stream_geometry(d, ts, it);
+    const uint8_t* raw = a.chunks[c].src + (size_t)g.j * d.blocksize;
+    if (g.ns > 1) gather_plane(ts, g.s, g.neblock, raw, win, lane, 32);
+    else filter_forward(a.p.filter, ts, g.bsize, raw, win, lane, 32);
     __syncwarp();
-    int32_t psize, csize;
-    bool stored = false;
-    if (warp_is_run(win, neblock, lane)) {
+    CItem r;
+    r.offset = 0;
+    r.stored = 0;
+    if (warp_is_run(win, g.neblock, lane)) {
       const uint8_t v = win[0];
-      csize = -(int32_t)v;
-      psize = v ? 1 : 0;
-      if (lane == 0 && v) out[0] = 0x01;
+      r.csize = -(int32_t)v;
+      r.psize = v ? 1 : 0;
     } else {
-      int hlog = 28 - __clz(neblock);                // floor(log2(neblock)) - 3: table bytes <= neblock / 4
+      int hlog = 28 - __clz(g.neblock);              // floor(log2(neblock)) - 3: table bytes <= neblock / 4
       const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
       hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
       const EncWork ew = enc_work(work, a.htab_bytes, hlog);
-      const int cap = neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
-      int r;
-      if (a.p.codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(win, neblock, out, cap, ew);
-      else r = lz_encode_warp<kCodecBlosclz>(win, neblock, out, cap, ew);
-      if (r <= 0 || r >= neblock) { stored = true; psize = csize = neblock; }
-      else psize = csize = r;
+      uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
+      const int cap = g.neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
+      int n;
+      if (a.p.codec == kCodecLz4) n = lz_encode_warp<kCodecLz4>(win, g.neblock, out, cap, ew);
+      else n = lz_encode_warp<kCodecBlosclz>(win, g.neblock, out, cap, ew);
+      if (n <= 0 || n >= g.neblock) { r.stored = 1; r.psize = r.csize = g.neblock; }
+      else r.psize = r.csize = n;
     }
-    // decoupled look-back over the earlier streams of this chunk
-    const int32_t total = 4 + psize;
-    const int first = d.item_base;
-    unsigned long long prefix = 0;
-    if (item > first) {
-      if (lane == 0) st_release_u64(&a.desc[item], kDescAggregate | (unsigned long long)total);
-      int look = item - 1;
-      for (;;) {
-        const int idx = look - lane;
-        unsigned long long v = kDescInclusive;  // lanes before the chunk start act as a zero inclusive prefix
-        if (idx >= first) {
-          for (;;) {
-            v = ld_acquire_u64(&a.desc[idx]);
-            if (v >> 62) break;
-            B2G_SPIN_PAUSE();
-          }
-        }
-        const unsigned inc = __ballot_sync(kFull, (v >> 62) == 2);
-        const int stop = inc ? __ffs((int)inc) - 1 : 31;
-        unsigned long long part = lane <= stop ? (v & kDescMask) : 0ull;
-        for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
-        prefix += part;
-        if (inc) break;
-        look -= 32;
-      }
+    if (lane == 0) a.items[item] = r;
+    __syncwarp();  // the window is free for the next item
+  }
+}
+
+// One CTA per chunk: exclusive scan of the stream sizes -> where every stream goes (blosc2.c:1956-1959 bstarts), the
+// chunk total, and the two whole-chunk outcomes (does not fit -> stored chunk; nothing but zero runs -> 32-byte chunk).
+struct PlaceArgs {
+  const DChunk* chunks;
+  const CInfo* info;
+  CItem* items;
+  CState* state;
+  int32_t n;
+};
+
+__global__ void __launch_bounds__(256) k_place(PlaceArgs a) {
+  int32_t* part = (int32_t*)dyn_smem();  // [blockDim.x] dynamic shared memory: 2 x blockDim.x ints
+  int32_t* nz = part + blockDim.x;
+  const int tid = (int)threadIdx.x, nt = (int)blockDim.x;
+  for (int c = (int)blockIdx.x; c < a.n; c += (int)gridDim.x) {
+    const CInfo d = a.info[c];
+    if (d.status < 0 || d.memcpyed) {
+      if (tid == 0) { CState st; st.overflow = 0; st.nonzero_streams = 0; st.done_blocks = 0; st.total = 0; a.state[c] = st; }
+      continue;
     }
-    int32_t off = kHdrExt + 4 * d.nblocks + (int32_t)prefix;
-    if (lane == 0) {
-      st_release_u64(&a.desc[item], kDescInclusive | (prefix + (unsigned long long)total));
-      const int32_t limit = min(ch.dst_cap, d.nbytes + kHdrExt);
-      if (off + total > limit) atomicExch(&a.state[c].overflow, 1);
-      else if (s == 0) st_le32(ch.dst + kHdrExt + 4 * j, off);
-      if (csize != 0) atomicAdd(&a.state[c].nonzero_streams, 1);
-      if (it == d.nitems - 1) a.state[c].total = off + total;
+    CItem* it = a.items + d.item_base;
+    const int per = (d.nitems + nt - 1) / nt;
+    const int lo = min(d.nitems, tid * per), hi = min(d.nitems, lo + per);
+    int32_t sum = 0, nonzero = 0;
+    for (int i = lo; i < hi; i++) { sum += 4 + it[i].psize; nonzero += it[i].csize != 0; }
+    __syncthreads();
+    part[tid] = sum;
+    nz[tid] = nonzero;
+    __syncthreads();
+    for (int o = 1; o < nt; o <<= 1) {  // inclusive scan over the thread partials
+      const int32_t v = tid >= o ? part[tid - o] : 0;
+      const int32_t w = tid >= o ? nz[tid - o] : 0;
+      __syncthreads();
+      part[tid] += v;
+      nz[tid] += w;
+      __syncthreads();
     }
-    if (off + total > min(ch.dst_cap, d.nbytes + kHdrExt)) continue;
-    // compaction: [csize][payload]
-    uint8_t* o = ch.dst + off;
-    if (lane == 0) st_le32(o, csize);
-    __syncwarp();  // the encoder's byte stores to the slab are visible to the whole warp
-    copy_bytes(o + 4, stored ? win : out, psize, lane, 32);
-    __syncwarp();  // window and slab are free for the next item
+    int32_t off = kHdrExt + 4 * d.nblocks + part[tid] - sum;
+    for (int i = lo; i < hi; i++) { it[i].offset = off; off += 4 + it[i].psize; }
+    if (tid == nt - 1) {
+      CState st;
+      st.total = kHdrExt + 4 * d.nblocks + part[tid];
+      st.nonzero_streams = nz[tid];
+      st.overflow = st.total > min(a.chunks[c].dst_cap, d.nbytes + kHdrExt) ? 1 : 0;
+      st.done_blocks = 0;
+      a.state[c] = st;
+    }
   }
 }
 
@@ -547,29 +578,38 @@ struct FinalizeArgs {
   const DChunk* chunks;
   const CInfo* info;
   const CState* state;
+  const CItem* items;
+  const uint8_t* scratch;
+  int64_t scratch_stride;
   DResult* res;
   const int32_t* base;
   int32_t n;
   int32_t total_items;
+  int32_t win_bytes;     // dynamic shared memory: a stored stream is re-filtered through it
   CParams p;
 };
 
-// One CTA per work item (block): chunk header by the chunk's first item, raw copy of every block of a memcpyed chunk.
+// One CTA per item number: the chunk header by the chunk's first item; the item's stream moved from its scratch slot to
+// its place in the chunk ([csize][payload], bstarts for the first stream of a block); for stored chunks the raw copy of
+// one block per item number.
 __global__ void __launch_bounds__(kCtaThreads) k_finalize(FinalizeArgs a) {
   const int tid = (int)threadIdx.x;
+  uint8_t* win = dyn_smem();
+  const int ts = a.p.typesize;
   for (int item = (int)blockIdx.x; item < a.total_items; item += (int)gridDim.x) {
     const int c = find_chunk(a.base, a.n, item, 0);
     const CInfo d = a.info[c];
     const DChunk ch = a.chunks[c];
-    const int j = item - d.item_base;
+    const int it = item - d.item_base;
     if (d.status < 0) {
-      if (j == 0 && tid == 0) { a.res[c].status = d.status; a.res[c].out_bytes = 0; }
+      if (it == 0 && tid == 0) { a.res[c].status = d.status; a.res[c].out_bytes = 0; }
       continue;
     }
     const CState st = a.state[c];
     const bool stored = d.memcpyed || st.overflow;
     const bool fits = !stored || d.nbytes + kHdrExt <= ch.dst_cap;
-    if (j == 0 && tid == 0) {
+    const bool zero = !stored && st.nonzero_streams == 0;
+    if (it == 0 && tid == 0) {
       uint8_t* h = ch.dst;
       int32_t cbytes = 0;
       if (fits) {
@@ -582,7 +622,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_finalize(FinalizeArgs a) {
         if (stored) {
           flags |= kFlagMemcpyed;
           cbytes = d.nbytes + kHdrExt;
-        } else if (st.nonzero_streams == 0) {
+        } else if (zero) {
           b2flags = 1 << 4;  // BLOSC2_SPECIAL_ZERO (blosc2.c:2520-2529)
           cbytes = kHdrExt;
         } else {
@@ -603,11 +643,34 @@ __global__ void __launch_bounds__(kCtaThreads) k_finalize(FinalizeArgs a) {
       a.res[c].status = 0;
       a.res[c].out_bytes = cbytes;  // 0 = does not fit, like blosc2_compress_ctx returning 0
     }
-    if (stored && fits && j < d.nblocks) {
-      const bool is_left = (j == d.nblocks - 1) && d.leftover > 0;
-      const int32_t bsize = is_left ? d.leftover : d.blocksize;
-      copy_bytes(ch.dst + kHdrExt + (size_t)j * d.blocksize, ch.src + (size_t)j * d.blocksize, bsize, tid,
-                 kCtaThreads);
+    if (stored) {
+      if (fits && it < d.nblocks) {
+        const bool is_left = (it == d.nblocks - 1) && d.leftover > 0;
+        const int32_t bsize = is_left ? d.leftover : d.blocksize;
+        copy_bytes(ch.dst + kHdrExt + (size_t)it * d.blocksize, ch.src + (size_t)it * d.blocksize, bsize, tid,
+                   kCtaThreads);
+      }
+      continue;
+    }
+    if (zero || it >= d.nitems) continue;
+    const CItem r = a.items[item];
+    const StreamGeom g = stream_geometry(d, ts, it);
+    uint8_t* o = ch.dst + r.offset;
+    if (tid == 0) {
+      st_le32(o, r.csize);
+      if (g.s == 0) st_le32(ch.dst + kHdrExt + 4 * g.j, r.offset);
+    }
+    if (r.stored) {  // the payload is the filtered stream: filter it again, straight from the source
+      const uint8_t* raw = ch.src + (size_t)g.j * d.blocksize;
+      __syncthreads();  // the previous item's copy has left the window
+      if (g.ns > 1) gather_plane(ts, g.s, g.neblock, raw, win, tid, kCtaThreads);
+      else filter_forward(a.p.filter, ts, g.bsize, raw, win, tid, kCtaThreads);
+      __syncthreads();
+      copy_bytes(o + 4, win, r.psize, tid, kCtaThreads);
+    } else if (r.csize < 0) {
+      if (tid == 0) o[4] = 0x01;  // run token (blosc2.c:1186-1199)
+    } else {
+      copy_bytes(o + 4, a.scratch + (size_t)item * (size_t)a.scratch_stride, r.psize, tid, kCtaThreads);
     }
   }
 }

@@ -82,22 +82,25 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   BatchCtl ctl[2];
   memset(ctl, 0, sizeof(ctl));
   ctl[0].total_items = (int32_t)items;
-  std::vector<unsigned long long> desc(items + 1, 0ull);
   const int warps = 2;  // independent workers per simulated CTA
   const int wwin = std::max((int)au(max_stream, 16), 1024);
-  const size_t stride = au((size_t)wwin + 512, 256);
-  std::vector<uint8_t> slab(stride * grid * warps + 256);
+  std::vector<CItem> citems(items + 1);
+  std::vector<uint8_t> scratch((size_t)wwin * items + 256);
   CompressArgs ca;
   ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
-  ca.desc = desc.data(); ca.slab = slab.data(); ca.slab_stride = (int64_t)stride; ca.n = n;
+  ca.items = citems.data(); ca.scratch = scratch.data(); ca.scratch_stride = wwin; ca.n = n;
   const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream);
   ca.win_bytes = wwin; ca.htab_bytes = htab_bytes; ca.p = p;
   const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + kEncWorkBytes);
   cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] { k_compress(ca); });
+  PlaceArgs pl;
+  pl.chunks = ch.data(); pl.info = info.data(); pl.items = citems.data(); pl.state = state.data(); pl.n = n;
+  cusim::launch(dim3(std::min(grid, n)), dim3(256), 2 * 256 * sizeof(int32_t), [&] { k_place(pl); });
   FinalizeArgs fa;
-  fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.res = res.data(); fa.base = base.data();
-  fa.n = n; fa.total_items = (int32_t)items; fa.p = p;
-  cusim::launch(dim3(std::min<int>(grid, (int)items)), dim3(kCtaThreads), 0, [&] { k_finalize(fa); });
+  fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.items = citems.data();
+  fa.scratch = scratch.data(); fa.scratch_stride = wwin; fa.res = res.data(); fa.base = base.data();
+  fa.n = n; fa.total_items = (int32_t)items; fa.win_bytes = wwin; fa.p = p;
+  cusim::launch(dim3(std::min<int>(grid, (int)items)), dim3(kCtaThreads), (size_t)wwin, [&] { k_finalize(fa); });
   for (int i = 0; i < n; i++) {
     status[i] = res[i].status;
     out[i] = res[i].status < 0 ? 0 : res[i].out_bytes;
