@@ -92,25 +92,45 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
     // Four groups of 32 positions per step, as four independent dependency chains (the step is latency-bound, not
     // issue-bound).  Within a step every position sees the table as it was before the step plus the earlier positions
     // of its own group; a first occurrence 32..127 bytes back inside the same step is the only candidate missed.
+    // The equal-hash resolution (__match_any_sync) has a long latency and depends only on the input bytes, not on the
+    // table: it is issued one step ahead, so that it completes under the previous step's verification work.
     unsigned myflags = 0;
-    for (int gb = 0; gb < 32; gb += 4) {
+    auto next_step = [&](int gb) {  // first step at or after gb that has to be probed, 32 = none
+      for (; gb < 32; gb += 4) {
+        const int bbase = tbase + gb * 32;
+        if (bbase > plimit) return 32;
+        if (bbase + 127 < ip) continue;
+        if (step > 1 && ((gb >> 2) & (step - 1))) continue;
+        return gb;
+      }
+      return 32;
+    };
+    uint32_t seq[4], h[4], nseqv[4], nh[4];
+    unsigned peers[4], npeers[4];
+    bool live[4], nlive[4];
+    auto fetch = [&](int gb, uint32_t* fs, uint32_t* fh, unsigned* fp, bool* fl) {
       const int bbase = tbase + gb * 32;
-      if (bbase > plimit) break;
-      if (bbase + 127 < ip) continue;
-      if (step > 1 && ((gb >> 2) & (step - 1))) continue;
-      uint32_t seq[4], h[4], tab[4];
-      unsigned peers[4];
-      bool live[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         const int p = bbase + 32 * j + lane;
-        live[j] = p <= plimit;
-        seq[j] = ld32_any(in + (live[j] ? p : 0));
-        h[j] = (seq[j] * 2654435761u) >> (32 - w.hlog);
-        tab[j] = w.htab[h[j]];
+        fl[j] = p <= plimit;
+        fs[j] = ld32_any(in + (fl[j] ? p : 0));
+        fh[j] = (fs[j] * 2654435761u) >> (32 - w.hlog);
       }
 #pragma unroll
-      for (int j = 0; j < 4; j++) peers[j] = match_any_u32(live[j] ? h[j] : (0x80000000u | (uint32_t)lane));
+      for (int j = 0; j < 4; j++) fp[j] = match_any_u32(fl[j] ? fh[j] : (0x80000000u | (uint32_t)lane));
+    };
+    int gb = next_step(0);
+    if (gb < 32) fetch(gb, nseqv, nh, npeers, nlive);
+    while (gb < 32) {
+      const int bbase = tbase + gb * 32;
+#pragma unroll
+      for (int j = 0; j < 4; j++) { seq[j] = nseqv[j]; h[j] = nh[j]; peers[j] = npeers[j]; live[j] = nlive[j]; }
+      const int gbn = next_step(gb + 4);
+      if (gbn < 32) fetch(gbn, nseqv, nh, npeers, nlive);
+      uint32_t tab[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) tab[j] = w.htab[h[j]];
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         const int p = bbase + 32 * j + lane;
@@ -136,6 +156,7 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       for (int j = 0; j < 4; j++)
         if (live[j] && (peers[j] >> lane) == 1u) w.htab[h[j]] = (uint16_t)(bbase + 32 * j + lane);  // last of its hash group
       __syncwarp();  // ... and every write before the next step's reads
+      gb = gbn;
     }
     __syncwarp();
     // ---- phase 2: greedy parse ------------------------------------------------------------------------------------

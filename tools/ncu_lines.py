@@ -48,7 +48,12 @@ def main():
     ia, isamp, iinst = hdr.index("Address"), hdr.index("# Samples"), hdr.index("Instructions Executed")
     stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_")]
     table = line_table(ksub)
-    body = [r for r in rows[hi + 1:] if len(r) > iinst and r[ia]]
+    body = []
+    for r in rows[hi + 1:]:
+        if r and r[0] in ("Address", "Kernel Name"):
+            break  # a second launch follows
+        if len(r) > iinst and r[ia]:
+            body.append(r)
     base = min(int(r[ia], 16) if r[ia].startswith("0x") else int(r[ia]) for r in body)
     agg = collections.defaultdict(lambda: [0, 0, collections.Counter()])
     tot_s = tot_i = 0
