@@ -14,4 +14,10 @@ ptxas:
 
 clean:
 	rm -f $(OUT)
-.PHONY: all clean ptxas
+.PHONY: all clean ptxas cpptest
+
+# C++20 host layer check: the reference's OIIO-free test cases on include/compressed/*.h + libb2g.so
+CPPTEST := tests/cpp/test_compressed
+cpptest: $(CPPTEST)
+$(CPPTEST): tests/cpp/test_compressed.cpp $(wildcard include/compressed/*.h include/compressed/blosc2/*.h) include/b2g.h $(OUT)
+	g++ -std=c++20 -O2 -Wall -Wextra -Iinclude -o $@ tests/cpp/test_compressed.cpp -Lcompressed_image_b200 -lb2g -Wl,-rpath,'$$ORIGIN/../../compressed_image_b200'

@@ -1,0 +1,221 @@
+// tests/cpp/test_compressed.cpp -- the reference's OpenImageIO-free C++ test cases, re-hosted on include/compressed/*.h
+// (which runs every chunk through libb2g.so on the GPU).  Mirrors:
+//   test/src/test_schunk.cpp:17-74        empty schunk; 4096 iota elements, chunk 256 B, block 64
+//   test/src/test_channel.cpp:20-125      size mismatch throws; 50- and 8192-element round trips; attribute getters;
+//                                         iterate-read and iterate-modify-reread
+//   test/src/test_chunk_span.cpp:16-57    x() / y() from the chunk index
+//   test/src/test_image.cpp:552-858       construct from vectors, chunk == / < / > data size, modify then re-read
+//   python/test/test_channel.py:173-237   get_chunk / set_chunk round trip and the exception types
+// Needs a CUDA device (there is no CPU path); run by tests/test_gpu_cpp.py under -m gpu.
+#include <cstdint>
+#include <cstdio>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "compressed/image.h"
+
+static int g_failed = 0, g_checks = 0;
+#define CHECK(cond)                                                                      \
+	do {                                                                                 \
+		++g_checks;                                                                      \
+		if (!(cond)) { ++g_failed; std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); } \
+	} while (0)
+#define CHECK_THROWS_AS(expr, type)                                                      \
+	do {                                                                                 \
+		++g_checks;                                                                      \
+		bool ok_ = false;                                                                \
+		try { expr; } catch (const type&) { ok_ = true; } catch (...) {}                 \
+		if (!ok_) { ++g_failed; std::printf("FAILED %s:%d: %s should throw %s\n", __FILE__, __LINE__, #expr, #type); } \
+	} while (0)
+
+namespace ci = compressed;
+
+template <typename T>
+static void test_schunk()
+{
+	{
+		ci::blosc2::schunk<T> super_chunk(128, 4096);
+		auto ctx = ci::blosc2::create_decompression_context(4);
+		CHECK(super_chunk.to_uncompressed(ctx).size() == 0);
+		CHECK(super_chunk.num_chunks() == 0);
+	}
+	std::vector<T> data(4096);
+	std::iota(data.begin(), data.end(), T{ 0 });
+	auto ctx = ci::blosc2::create_compression_context<T>(4, ci::enums::codec::lz4, 9, 128);
+	ci::blosc2::schunk<T> super_chunk(std::span<const T>(data), 64, 256, ctx);
+	auto dctx = ci::blosc2::create_decompression_context(4);
+	auto decompressed = super_chunk.to_uncompressed(dctx);
+	CHECK(decompressed.size() == 4096);
+	CHECK(decompressed == data);
+	CHECK(super_chunk.num_chunks() == 4096 * sizeof(T) / 256);
+	CHECK(super_chunk.byte_size() / sizeof(T) == 4096);
+	CHECK(super_chunk.chunk(dctx, 0).size() == 256 / sizeof(T));
+	CHECK_THROWS_AS(super_chunk.chunk(dctx, super_chunk.num_chunks()), std::out_of_range);
+}
+
+template <typename T>
+static void test_channel_roundtrip(ci::enums::codec codec)
+{
+	std::vector<T> small(50, static_cast<T>(25));
+	ci::channel<T> ch_small(std::span<const T>(small), 10, 5, codec);
+	CHECK(ch_small.get_decompressed() == small);
+
+	std::vector<T> data(8192);
+	for (size_t i = 0; i < data.size(); ++i) data[i] = static_cast<T>((i * 7) % 251);
+	ci::channel<T> ch(std::span<const T>(data), 128, 64, codec, 5, 128, 4096);
+	CHECK(ch.get_decompressed() == data);
+	CHECK(ch.width() == 128);
+	CHECK(ch.height() == 64);
+	CHECK(ch.compression() == codec);
+	CHECK(ch.compression_level() == 5);
+	CHECK(ch.uncompressed_size() == 8192);
+	CHECK(ch.chunk_size() == 4096 / (128 * sizeof(T)) * (128 * sizeof(T)));
+	CHECK(ch.num_chunks() == (8192 * sizeof(T) + ch.chunk_size() - 1) / ch.chunk_size());
+	CHECK(ch.compressed_bytes() > 0);
+
+	// get_chunk / set_chunk over all chunks, buffers of the wrong size and bad indices
+	for (size_t i = 0; i < ch.num_chunks(); ++i)
+	{
+		std::vector<T> buf(ch.chunk_elems(i));
+		ch.get_chunk(std::span<T>(buf), i);
+		for (auto& v : buf) v = static_cast<T>(v + 1);
+		ch.set_chunk(std::span<T>(buf), i);
+	}
+	auto after = ch.get_decompressed();
+	bool all_plus_one = true;
+	for (size_t i = 0; i < data.size(); ++i) all_plus_one = all_plus_one && after[i] == static_cast<T>(data[i] + 1);
+	CHECK(all_plus_one);
+	std::vector<T> wrong(ch.chunk_elems(0) + 1);
+	CHECK_THROWS_AS(ch.get_chunk(std::span<T>(wrong), 0), std::invalid_argument);
+	CHECK_THROWS_AS(ch.set_chunk(std::span<T>(wrong), 0), std::invalid_argument);
+	std::vector<T> right(ch.chunk_elems(0));
+	CHECK_THROWS_AS(ch.get_chunk(std::span<T>(right), ch.num_chunks()), std::out_of_range);
+	CHECK_THROWS_AS(ch.set_chunk(std::span<T>(right), ch.num_chunks()), std::out_of_range);
+
+	// batched chunk access: all chunks in one launch each way
+	std::vector<std::vector<T>> bufs;
+	std::vector<std::span<T>> spans;
+	std::vector<std::span<const T>> cspans;
+	std::vector<size_t> idx;
+	for (size_t i = 0; i < ch.num_chunks(); ++i) { bufs.emplace_back(ch.chunk_elems(i)); idx.push_back(i); }
+	for (auto& b : bufs) { spans.emplace_back(b); }
+	ch.get_chunks(idx, spans);
+	for (auto& b : bufs) { for (auto& v : b) v = static_cast<T>(v - 1); cspans.emplace_back(b.data(), b.size()); }
+	ch.set_chunks(idx, cspans);
+	CHECK(ch.get_decompressed() == data);
+}
+
+static void test_channel_misc()
+{
+	std::vector<uint16_t> data(100);
+	CHECK_THROWS_AS(ci::channel<uint16_t>(std::span<const uint16_t>(data), 20, 20), std::runtime_error);
+	CHECK_THROWS_AS(ci::channel<uint16_t>(std::span<const uint16_t>(data), 10, 10, ci::enums::codec::lz4, 9, 64, 8),
+		std::runtime_error);  // a scanline does not fit the chunk size
+
+	// iterate and read, then iterate, modify and re-read (test_channel.cpp:92-125)
+	std::vector<uint16_t> vec(128);
+	std::iota(vec.begin(), vec.end(), uint16_t{ 0 });
+	ci::channel<uint16_t> ch(std::span<const uint16_t>(vec), 16, 8, ci::enums::codec::lz4, 9, 64, 64);
+	CHECK(ch.num_chunks() == 4);
+	size_t seen = 0;
+	for (auto chunk : ch)
+	{
+		for (size_t i = 0; i < chunk.size(); ++i)
+		{
+			CHECK(chunk[i] == vec[seen]);
+			CHECK(chunk.x(i) == seen % 16);
+			CHECK(chunk.y(i) == seen / 16);
+			++seen;
+		}
+	}
+	CHECK(seen == 128);
+	for (auto chunk : ch) for (auto& v : chunk) v = static_cast<uint16_t>(v * 2);
+	auto doubled = ch.get_decompressed();
+	bool ok = true;
+	for (size_t i = 0; i < vec.size(); ++i) ok = ok && doubled[i] == vec[i] * 2;
+	CHECK(ok);
+	auto it = ch.end();
+	CHECK_THROWS_AS(++it, std::out_of_range);
+
+	// lazy channels: nothing compressed until written (channel.h:219-304, python/test/test_channel.py:92-170)
+	auto z = ci::channel<float>::zeros(64, 64, ci::enums::codec::blosclz, 2, 256, 1024);
+	CHECK(z.compressed_bytes() == z.num_chunks() * sizeof(float));
+	CHECK(z.get_decompressed() == std::vector<float>(64 * 64, 0.0f));
+	auto f = ci::channel<float>::full_like(z, 7.5f);
+	CHECK(f.get_decompressed() == std::vector<float>(64 * 64, 7.5f));
+	std::vector<float> buf(f.chunk_elems(1), 1.0f);
+	f.set_chunk(std::span<float>(buf), 1);
+	auto mixed = f.get_decompressed();
+	CHECK(mixed[0] == 7.5f);
+	CHECK(mixed[f.chunk_elems(0)] == 1.0f);
+	CHECK(f.compressed_bytes() > f.num_chunks() * sizeof(float));
+}
+
+template <typename T>
+static void test_image(size_t chunk_size)
+{
+	const size_t w = 32, h = 16;
+	std::vector<std::vector<T>> chans(3, std::vector<T>(w * h));
+	for (size_t c = 0; c < 3; ++c)
+		for (size_t i = 0; i < w * h; ++i) chans[c][i] = static_cast<T>(i * (c + 1));
+	ci::image<T> img(chans, w, h, { "R", "G", "B" }, ci::enums::codec::lz4, 9, 256, chunk_size);
+	CHECK(img.num_channels() == 3);
+	CHECK(img.width() == w);
+	CHECK(img.height() == h);
+	CHECK(img.get_decompressed() == chans);
+	CHECK(img.channel("G").get_decompressed() == chans[1]);
+	CHECK(img.channel(2).get_decompressed() == chans[2]);
+	CHECK(img.get_channel_offset("B") == 2);
+	CHECK_THROWS_AS(img.channel(3), std::out_of_range);
+	CHECK_THROWS_AS(img.channel("A"), std::invalid_argument);
+	CHECK(img.compression_ratio() > 0.0);
+	// modify every channel through chunk iteration, re-read (test_image.cpp:780-858 does this through zip)
+	for (auto& ch : img.channels())
+		for (auto chunk : ch) for (auto& v : chunk) v = static_cast<T>(v + 3);
+	auto out = img.get_decompressed();
+	bool ok = true;
+	for (size_t c = 0; c < 3; ++c)
+		for (size_t i = 0; i < w * h; ++i) ok = ok && out[c][i] == static_cast<T>(chans[c][i] + 3);
+	CHECK(ok);
+	// add / extract / remove
+	std::vector<T> alpha(w * h, static_cast<T>(1));
+	img.add_channel(std::span<const T>(alpha), w, h, "A");
+	CHECK(img.num_channels() == 4);
+	CHECK(img.channel("A").get_decompressed() == alpha);
+	CHECK_THROWS_AS(img.add_channel(std::span<const T>(alpha), w / 2, h * 2, "X"), std::invalid_argument);
+	auto r = img.extract_channel("R");
+	CHECK(r.width() == w);
+	img.remove_channel(0);
+	CHECK(img.num_channels() == 2);
+	CHECK(img.channelnames() == (std::vector<std::string>{ "B", "A" }));
+}
+
+int main()
+{
+	if (b2g_device_count() < 1)
+	{
+		std::printf("no CUDA device: compressed::* has no CPU path\n");
+		try { auto ctx = compressed::blosc2::create_decompression_context(1); } catch (const std::runtime_error& e)
+		{
+			std::printf("create_decompression_context failed loudly as expected: %s\n", e.what());
+			return 3;
+		}
+		return 2;
+	}
+	test_schunk<uint8_t>(); test_schunk<uint16_t>(); test_schunk<uint32_t>(); test_schunk<float>();
+	for (auto codec : { compressed::enums::codec::lz4, compressed::enums::codec::blosclz })
+	{
+		test_channel_roundtrip<uint8_t>(codec); test_channel_roundtrip<int8_t>(codec);
+		test_channel_roundtrip<uint16_t>(codec); test_channel_roundtrip<int16_t>(codec);
+		test_channel_roundtrip<uint32_t>(codec); test_channel_roundtrip<int32_t>(codec);
+		test_channel_roundtrip<float>(codec);
+	}
+	test_channel_misc();
+	for (size_t chunk : { size_t(32 * 16 * 4), size_t(1024), size_t(768), size_t(4194304) })
+	{
+		test_image<uint8_t>(chunk); test_image<uint16_t>(chunk); test_image<float>(chunk);
+	}
+	std::printf("%d checks, %d failed\n", g_checks, g_failed);
+	return g_failed ? 1 : 0;
+}
