@@ -66,6 +66,8 @@ struct HostBuf {  // pinned
 };
 
 constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
+// B2G_TWO_PHASE=0 turns the parse + record-replay decode off (developer switch: A/B timing of the one-pass decoder)
+const bool g_two_phase = [] { const char* e = getenv("B2G_TWO_PHASE"); return !(e && e[0] == '0'); }();
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -79,13 +81,15 @@ struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab;
+  cudaEvent_t ev_mid = nullptr;                      // between k_parse and k_decode (B2G_TIMING=1)
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_itab, d_rec;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
   void release() {
-    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab}) b->release();
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_itab, &d_rec}) b->release();
     for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     if (res_ready) cudaEventDestroy(res_ready);
+    if (ev_mid) cudaEventDestroy(ev_mid);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -183,7 +187,7 @@ struct DecGeom {
 int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
   if (stream_bytes > 96 * 1024) stream_bytes = 16 * 1024;  // such streams decode through the global slab anyway
   g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1)), 1024);
-  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : 0);
+  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : kSeqGroupSmem);  // + the record executor's scratch
   int best = 0;
   g.warps = 1;
   for (int w : {1, 2, 3, 4, 6, 8}) {
@@ -220,6 +224,19 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   if (int rc = L.d_base.ensure(sizeof(int32_t) * 2 * ((size_t)n + 1))) return rc;
   if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
   if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  // two-phase decode (k_parse -> records -> k_decode): one ItemRec per stream item, 8-byte sequence records in regions
+  // of cbytes / 2 + 2 per chunk (k_plan_decode lays them out; chunks that do not fit fall back to the one-pass decoder)
+  int64_t itab_cap = 0, rec_cap = 0;
+  const int hint_block = std::max(std::min(c->p.blocksize, c->blocksize), 1024);
+  for (int i = 0; i < n; i++) {
+    const int64_t cap = std::max(h_desc[i].dst_cap, 0);
+    itab_cap += (cap / hint_block + 2) * kMaxStreams;
+    rec_cap += std::min<int64_t>(std::max(h_desc[i].src_bytes, 0), cap + B2G_MAX_OVERHEAD) / 2 + 2;
+  }
+  itab_cap = std::min<int64_t>(itab_cap, (int64_t)1 << 27);
+  if (!g_two_phase) itab_cap = rec_cap = 0;
+  if (int rc = L.d_itab.ensure(sizeof(ItemRec) * (size_t)itab_cap + 16)) return rc;
+  if (int rc = L.d_rec.ensure(sizeof(uint2) * (size_t)rec_cap + 16)) return rc;
   CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaEventRecord(L.ev[0], s));
   PlanArgs pa;
@@ -231,7 +248,8 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   pa.n = n;
   pa.max_block = std::max(c->blocksize, c->p.blocksize);
   pa.zstd_ok = want_zstd ? 1 : 0;
-  k_plan_decode<<<1, 1024, 2 * 1024 * sizeof(int32_t), s>>>(pa);
+  pa.rec_cap = rec_cap;
+  k_plan_decode<<<1, kPlanThreads, kPlanSmemBytes, s>>>(pa);
   c->launches++;
   CU(cudaEventRecord(L.ev[1], s));
   DecodeArgs da;
@@ -245,6 +263,14 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.wstride = g.wstride;
   da.slab = (uint8_t*)L.d_slab.p;
   da.slab_stride = (int64_t)slab_stride(c);
+  da.itab = itab_cap > 0 ? (ItemRec*)L.d_itab.p : nullptr;
+  da.itab_cap = (int32_t)itab_cap;
+  da.rec = (uint2*)L.d_rec.p;
+  if (itab_cap > 0) {
+    k_parse<<<c->sms * 6, kParseThreads, kParseSmemBytes, s>>>(da);
+    c->launches++;
+  }
+  CU(cudaEventRecord(L.ev_mid, s));
   k_decode<false><<<g.grid, 32 * g.warps, g.smem, s>>>(da);
   c->launches++;
   if (want_zstd) {
@@ -363,6 +389,12 @@ int finish(b2g_ctx* c, Lane& L, b2g_chunk* chunks, int n) {
   float a = 0, b = 0;
   if (cudaEventElapsedTime(&a, L.ev[0], L.ev[1]) == cudaSuccess) c->last_ms[0] += a;
   if (cudaEventElapsedTime(&b, L.ev[1], L.ev[2]) == cudaSuccess) c->last_ms[1] += b;
+  static const bool timing = [] { const char* e = getenv("B2G_TIMING"); return e && e[0] == '1'; }();
+  if (timing) {  // developer switch: the parse / replay split of a decode batch
+    float m = 0;
+    if (cudaEventElapsedTime(&m, L.ev[1], L.ev_mid) == cudaSuccess && m > 0)
+      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms\n", a, m, b - m);
+  }
   return 0;
 }
 
@@ -396,6 +428,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
     ok = !cuda_fail(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking), "cudaStreamCreate");
     for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&L.ev[i]), "cudaEventCreate");
     if (ok) ok = !cuda_fail(cudaEventCreateWithFlags(&L.res_ready, cudaEventDisableTiming), "cudaEventCreate");
+    if (ok) ok = !cuda_fail(cudaEventCreate(&L.ev_mid), "cudaEventCreate");
   }
   c->stream_hint = c->p.blocksize / plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, c->p.blocksize);
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;

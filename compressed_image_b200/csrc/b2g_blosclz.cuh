@@ -52,7 +52,8 @@ __device__ __forceinline__ int blosclz_decode_warp_t(const uint8_t* in, int n, u
       if (op + run > cap) return 0;
       if (ip + run > n) return 0;
       const uint32_t nctrl = ip + run < n ? in[ip + run] : 0u;  // read before the run is written: in place, the run
-      lz_literal_copy<INPLACE>(out, op, in, ip, run, a + ip - op, lane);  // may end right below it
+      if (INPLACE) __syncwarp();  // may end right below it, and the NEXT run may start on it: every lane has read it
+      lz_literal_copy<INPLACE>(out, op, in, ip, run, a + ip - op, lane);
       op += run;
       ip += run;
       if (ip >= n) break;

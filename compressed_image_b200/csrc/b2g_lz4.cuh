@@ -93,12 +93,14 @@ __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8
       t1 = ipn + 1 < n ? in[ipn + 1] : 0u;
     }
     ml += 4;
-    if ((int)offset > cpy || offset == 0) return -1;
+    if ((int)offset > cpy) return -1;
     const int mend = cpy + ml;
     if (mend > cap - 5) return -1;  // lz4.c:2419-2423: the last 5 bytes are always literals
     if (INPLACE && mend > a + ipn) return -2;
     __syncwarp();                   // literals (and every earlier match) visible before the match is read
-    if (ml <= 32 && (int)offset >= ml) { if (lane < ml) out[cpy + lane] = out[cpy - (int)offset + lane]; }
+    if (offset == 0) fill_bytes(out + cpy, 0, ml, lane, 32);  // accepted by LZ4_decompress_safe: the match reads itself
+                                                              // after lz4.c:500 / :2407 zeroed its first word -> zeros
+    else if (ml <= 32 && (int)offset >= ml) { if (lane < ml) out[cpy + lane] = out[cpy - (int)offset + lane]; }
     else lz_match_copy(out, cpy, (int)offset, ml, lane);
     op = mend;
     ip = ipn;

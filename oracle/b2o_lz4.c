@@ -202,9 +202,11 @@ int b2o_lz4_decompress(const uint8_t* src, int n, uint8_t* dst, int cap) {
     if (cpy > oend - MFLIMIT) { /* L4:2419-2423 */
       if (cpy > oend - LASTLITERALS) return -1;
     }
-    if (offset == 0) { /* reference copies indeterminate bytes from op itself; we define it as zeros-in-place */
-      /* (never produced by a valid encoder) */
-    }
+    if (offset == 0) { /* accepted by the reference: the match reads itself after L4:500 / L4:2407 wrote a zero word
+                          at its start, so it comes out as zeros (never produced by a valid encoder; pinned against
+                          the reference in tests/test_oracle.py) */
+      memset(dst + op, 0, (size_t)length);
+    } else
     for (long k = 0; k < length; k++) dst[op + k] = dst[match + k];
     op = (int)cpy;
   }

@@ -117,3 +117,36 @@ def test_malformed_chunks_agree_with_reference():
         assert _libs.ref_decompress(bad)[0] < 0 and _libs.oracle_decompress(bad)[0] < 0
         rc, _ = _libs.oracle_decompress(chunk, cap=src.size - 1)
         assert rc < 0 and _libs.ref_decompress(chunk, cap=src.size - 1)[0] < 0
+
+
+def _lz4_offset0_stream(ml, tail=12):
+    """8 literals, a match with OFFSET 0 of length ml, then `tail` last literals."""
+    out = bytearray()
+    mlc = ml - 4
+    out.append((8 << 4) | min(mlc, 15))
+    out += b"abcdefgh" + bytes([0, 0])
+    if mlc >= 15:
+        r = mlc - 15
+        while r >= 255:
+            out.append(255)
+            r -= 255
+        out.append(r)
+    out.append(tail << 4)
+    out += bytes(range(65, 65 + tail))
+    return np.frombuffer(bytes(out), dtype=np.uint8).copy(), 8 + ml + tail
+
+
+@pytest.mark.skipif(_libs.ref() is None, reason="reference library not built")
+@pytest.mark.parametrize("ml", [4, 5, 8, 9, 16, 18, 19, 32, 33, 64, 300, 1000])
+def test_lz4_offset_zero_is_zeros_like_the_reference(ml):
+    """LZ4_decompress_safe accepts a match offset of 0 (lz4.c:2356 only rejects offsets beyond the prefix) and the match
+    comes out as zeros whatever the destination held before (lz4.c:500, :2407).  Pins the oracle's reading of it."""
+    s, cap = _lz4_offset0_stream(ml)
+    for fill in (0xAB, 0x00):
+        a = np.full(cap + 8, fill, np.uint8)
+        b = np.full(cap + 8, fill, np.uint8)
+        ra = _libs.ref().ref_lz4_decompress(s.ctypes.data, int(s.size), a.ctypes.data, cap)
+        rb = _libs.oracle().b2o_lz4_decompress(s.ctypes.data, int(s.size), b.ctypes.data, cap)
+        assert ra == rb == cap
+        assert np.array_equal(a, b)
+        assert not a[8:8 + ml].any()

@@ -220,6 +220,102 @@ def test_decode_special_chunks():
             assert np.array_equal(_libs.ref_decompress(ch)[1], exp)
 
 
+@pytest.mark.parametrize("ml", [4, 9, 19, 33, 300])
+def test_lz4_offset_zero_stream(ml):
+    """A match offset of 0 decodes to zeros (the reference accepts it: tests/test_oracle.py pins that)."""
+    from test_oracle import _lz4_offset0_stream
+    s, cap = _lz4_offset0_stream(ml)
+    exp = np.zeros(cap, np.uint8)
+    assert _libs.oracle().b2o_lz4_decompress(s.ctypes.data, int(s.size), exp.ctypes.data, cap) == cap
+    r, out = _sim.stream_decode(_data.FMT_LZ4 if hasattr(_data, "FMT_LZ4") else 1, s, cap)
+    assert r == cap and np.array_equal(out, exp)
+
+
+# ---- two-phase decode (k_parse -> sequence records -> replay) ---------------------------------------------------------
+def test_two_phase_is_taken_and_equals_one_pass():
+    """lz4 / blosclz reference chunks go through the record path (counted), and decode identically with it switched off
+    or short of record space."""
+    keys = [k for k in _golden.REF_KEYS if "_c%d_" % _data.LZ4 in k or "_c%d_" % _data.BLOSCLZ in k]
+    chunks = [_golden.ref_chunk(k) for k in keys]
+    h0 = _sim.lib().sim_two_phase_hits()
+    res1 = _sim.decompress_batch(chunks, grid=3, two_phase=1)
+    h1 = _sim.lib().sim_two_phase_hits()
+    res0 = _sim.decompress_batch(chunks, grid=3, two_phase=0)
+    h2 = _sim.lib().sim_two_phase_hits()
+    res2 = _sim.decompress_batch(chunks, grid=3, two_phase=2)
+    h3 = _sim.lib().sim_two_phase_hits()
+    assert h1 - h0 > 100 and h2 == h1 and 0 < h3 - h2 < h1 - h0
+    for k, a, b, c in zip(keys, res1, res0, res2):
+        exp = _data.make_case(_golden.MANIFEST["ref_chunks"][k]["case"])
+        assert a[0] == 0 and b[0] == 0 and c[0] == 0, k
+        assert np.array_equal(a[1], exp) and np.array_equal(b[1], exp) and np.array_equal(c[1], exp), k
+
+
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+def test_two_phase_same_decisions_on_damaged_payloads(codec):
+    """Byte flips all over the payload: the record path and the one-pass decoder agree with the oracle on accept /
+    reject, and on every byte when the damaged chunk still decodes."""
+    rng = np.random.default_rng(7 + codec)
+    key = [k for k in _golden.REF_KEYS if k.startswith("text_n300000") and "_c%d_" % codec in k][0]
+    chunk = _golden.ref_chunk(key)
+    nbytes = 300000
+    bad = []
+    for _ in range(40):
+        b = chunk.copy()
+        for _ in range(int(rng.integers(1, 4))):
+            b[int(rng.integers(32, chunk.size))] ^= np.uint8(rng.integers(1, 256))
+        bad.append(b)
+    r1 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad), two_phase=1)
+    r0 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad), two_phase=0)
+    for i in range(len(bad)):
+        rc, exp = _libs.oracle_decompress(bad[i], cap=nbytes)
+        assert (r1[i][0] < 0) == (rc < 0) and (r0[i][0] < 0) == (rc < 0), (i, r1[i][0], r0[i][0], rc)
+        assert r1[i][0] == r0[i][0]
+        if rc >= 0:
+            assert np.array_equal(r1[i][1], exp) and np.array_equal(r0[i][1], exp)
+
+
+def test_two_phase_gpu_compressed_chunks():
+    """Chunks from the simulated GPU encoder (long runs, overlapping matches, tiny tails) through the record path."""
+    srcs = [_data.make_data(k, n, ts, seed=n) for k in ("iota", "sparse", "text", "f32", "zeros")
+            for n, ts in ((70001, 1), (131072, 2), (65536 + 24, 4))]
+    for codec, filt in ((_data.LZ4, _data.SHUFFLE), (_data.BLOSCLZ, _data.BITSHUFFLE), (_data.BLOSCLZ, _data.SHUFFLE)):
+        for ts in (1, 2, 4):
+            mine = [s for s in srcs if s.size % ts == 0][:6]
+            enc = _sim.compress_batch(mine, codec, 9, ts, filt, 32768)
+            h0 = _sim.lib().sim_two_phase_hits()
+            dec = _sim.decompress_batch([c for _, c in enc], two_phase=1, win_bytes=34816)
+            assert _sim.lib().sim_two_phase_hits() > h0, (codec, filt, ts)
+            for s, (st, out) in zip(mine, dec):
+                assert st == 0 and np.array_equal(out, s.view(np.uint8).reshape(-1))
+
+
+def _noisy_with_repeats(n, gap, mlen, seed):
+    """Random bytes with a short repeat of earlier bytes every `gap` bytes: long literal runs, barely compressible, so
+    an in-place decode runs with its output right behind the unread input."""
+    r = np.random.default_rng(seed)
+    a = r.integers(0, 256, size=n, dtype=np.uint8)
+    for p in range(gap, n - mlen - 16, gap):
+        back = int(r.integers(1, min(p, 60000)))
+        a[p:p + mlen] = a[p - back:p - back + mlen]
+    return a
+
+
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+@pytest.mark.parametrize("gap,mlen", [(40, 12), (70, 8), (200, 24), (33, 5), (1000, 40)])
+def test_two_phase_long_literal_runs_in_place(codec, gap, mlen):
+    srcs = [_noisy_with_repeats(65536, gap, mlen, seed) for seed in (1, 2)]
+    for ts, bs in ((1, 16384), (2, 32768), (1, 32768)):
+        enc = _sim.compress_batch(srcs, codec, 9, ts, _data.SHUFFLE, bs)
+        chunks = [c for _, c in enc]
+        exp = [_libs.oracle_decompress(c)[1] for c in chunks]
+        for wb in (17040, 34000):
+            h0 = _sim.lib().sim_two_phase_hits()
+            dec = _sim.decompress_batch(chunks, two_phase=1, win_bytes=wb)
+            for s, e, (st, out) in zip(srcs, exp, dec):
+                assert st == 0 and np.array_equal(out, s) and np.array_equal(e, s), (ts, bs, wb)
+
+
 # ---- whole chunks: compress -----------------------------------------------------------------------------------------
 def _compress_cases():
     seen = set()
