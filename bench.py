@@ -273,9 +273,21 @@ def run_b2g(args, rank, world, local_rank):
     hcomp = ctx.make_batch([h_raw.data_ptr() + raw_off[i] for i in order], [h_cout.data_ptr() + i * slot for i in order],
                            [int(pieces[i].size) for i in order], [CHUNK + 32] * n)
 
+    # The get_chunk pass and the set_chunk pass are independent batches (decode reads the stored chunks, encode reads the
+    # raw image): they go to two contexts through the asynchronous C-ABI calls, so the D2H-heavy decode and the H2D-heavy
+    # encode share the PCIe link in both directions.  B2G_E2E_SERIAL=1 runs them one after the other instead.
+    ctx2 = _b2g.Context(LZ4, CLEVEL, TYPESIZE, SHUFFLE, BLOCK, local_rank)
+    serial = os.environ.get("B2G_E2E_SERIAL") == "1"
+
     def e2e_step():
-        ctx.decompress_batch(hdec, stream=sh)
-        ctx.compress_batch(hcomp, stream=sh)
+        if serial:
+            ctx.decompress_batch(hdec, stream=sh)
+            ctx.compress_batch(hcomp, stream=sh)
+            return
+        ctx.decompress_batch_async(hdec)
+        ctx2.compress_batch_async(hcomp)
+        ctx2.wait()
+        ctx.wait()
 
     e2e_steps = max(3, min(args.steps, 10))
     if args.kernels_only:
@@ -301,7 +313,9 @@ def run_b2g(args, rank, world, local_rank):
     cout_total = sum(hcomp[k].out_bytes for k in range(n))
     e2e = {"value": world * 2 * nbytes_total / (e2e_ms * 1e-3) / 1e9, "unit": "GB/s",
            "h2d_bytes_per_step": cbytes_total + nbytes_total, "d2h_bytes_per_step": nbytes_total + cout_total,
-           "ms_per_step": e2e_ms, "steps": e2e_steps, "host_buffers": "pinned"}
+           "ms_per_step": e2e_ms, "steps": e2e_steps, "host_buffers": "pinned",
+           "calls": "b2g_decompress_batch + b2g_compress_batch, one after the other" if serial else
+                    "b2g_decompress_batch_async (ctx A) + b2g_compress_batch_async (ctx B) + b2g_wait x2"}
 
     if rank != 0:
         if dist:

@@ -52,7 +52,7 @@ def lib():
         L.b2g_destroy.argtypes = [vp]
         L.b2g_destroy.restype = None
         for f in ("b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_device",
-                  "b2g_decompress_batch_device"):
+                  "b2g_decompress_batch_device", "b2g_compress_batch_async", "b2g_decompress_batch_async"):
             getattr(L, f).argtypes = [vp, pc, ci, vp]
             getattr(L, f).restype = ci
         L.b2g_wait.argtypes = [vp]
@@ -70,7 +70,8 @@ def lib():
     return _lib
 
 
-EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_device",
+EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
+           "b2g_decompress_batch_async", "b2g_compress_batch_device",
            "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 
@@ -137,6 +138,13 @@ class Context:
 
     def decompress_batch(self, batch, n=None, stream=None):
         self._call(lib().b2g_decompress_batch, batch, len(batch) if n is None else n, stream)
+
+    def compress_batch_async(self, batch, n=None):
+        """Host pointers, enqueued only: `batch` and its buffers must stay alive until wait()."""
+        self._call(lib().b2g_compress_batch_async, batch, len(batch) if n is None else n, None)
+
+    def decompress_batch_async(self, batch, n=None):
+        self._call(lib().b2g_decompress_batch_async, batch, len(batch) if n is None else n, None)
 
     def compress_batch_device(self, batch, n=None, stream=None):
         self._call(lib().b2g_compress_batch_device, batch, len(batch) if n is None else n, stream)

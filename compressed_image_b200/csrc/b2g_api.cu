@@ -66,8 +66,10 @@ struct HostBuf {  // pinned
 };
 
 constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
-// B2G_TWO_PHASE=0 turns the parse + record-replay decode off (developer switch: A/B timing of the one-pass decoder)
-const bool g_two_phase = [] { const char* e = getenv("B2G_TWO_PHASE"); return !(e && e[0] == '0'); }();
+// B2G_TWO_PHASE=1 (read when a context is created) decodes lz4 / blosclz streams in two phases: k_parse (one lane per
+// stream -> sequence records) + record replay in k_decode.  Off by default: on the bench image the replay (0.62 ms) plus
+// the parse (0.30 ms) is slower than the one-pass warp decoder (0.71 ms); see DESIGN.md section 4.
+bool env_two_phase() { const char* e = getenv("B2G_TWO_PHASE"); return e && e[0] == '1'; }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -76,7 +78,8 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // One pipeline lane: a stream plus every per-batch work buffer, so that sub-batches of a host-pointer call can be in
 // flight on different lanes at once (H2D of one overlapping the kernels of another and the D2H of a third).  The
 // device-resident entry points use lane 0 on the caller's stream.
-constexpr int kLanes = 3;
+constexpr int kLanes = 6;  // lanes a context owns; host-pointer batches rotate over the first g_lanes of them
+static const int g_lanes = [] { const char* e = getenv("B2G_LANES"); int v = e ? atoi(e) : 6; return v < 1 ? 1 : (v > kLanes ? kLanes : v); }();
 struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
@@ -106,12 +109,24 @@ struct b2g_ctx {
   int win_bytes = 32768;   // shared-memory window (standalone filters)
   int max_grid_warps = 0;  // most worker warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
+  bool two_phase = false;  // B2G_TWO_PHASE=1 at creation
   // device + pinned work buffers
   DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
-  // in-flight batch (device-resident API)
+  // in-flight batch (device-resident API, or an asynchronous host-pointer batch)
   b2g_chunk* pend = nullptr;
   int pend_n = 0;
   cudaStream_t pend_stream = nullptr;
+  int pend_kind = 0;                 // 0 device-resident, 1 host decompress, 2 host compress
+  std::vector<int> pend_bounds;      // sub-batch boundaries of the host-pointer batch in flight
+  std::vector<size_t> pend_out_off;  // compress: where each chunk sits in d_out
+  std::vector<int> pend_order;       // batch position -> index into the caller's array (batches are processed in host
+                                     // address order so that neighbouring buffers move with one copy)
+  // host-pointer batches: pinned descriptor / plan / result arrays for the WHOLE batch (sub-batches use slices, so
+  // nothing the copy engines still have to read is ever overwritten), one event per sub-batch, and a stream of its own
+  // for the size-dependent D2H copies of compress
+  HostBuf h_desc_all, h_res_all, h_cinfo_all, h_base_all;
+  std::vector<cudaEvent_t> sub_done;
+  cudaStream_t d2h_stream = nullptr;
 };
 
 namespace {
@@ -210,7 +225,8 @@ int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
   return 0;
 }
 
-int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd, int stream_bytes) {
+int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd, int stream_bytes,
+                   DResult* h_res = nullptr) {
   DecGeom g, gz;
   if (int rc = decode_geometry(c, stream_bytes, false, g)) return rc;
   gz = g;
@@ -223,7 +239,10 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
   if (int rc = L.d_base.ensure(sizeof(int32_t) * 2 * ((size_t)n + 1))) return rc;
   if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
-  if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (!h_res) {
+    if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+    h_res = (DResult*)L.h_res.p;
+  }
   // two-phase decode (k_parse -> records -> k_decode): one ItemRec per stream item, 8-byte sequence records in regions
   // of cbytes / 2 + 2 per chunk (k_plan_decode lays them out; chunks that do not fit fall back to the one-pass decoder)
   int64_t itab_cap = 0, rec_cap = 0;
@@ -234,7 +253,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     rec_cap += std::min<int64_t>(std::max(h_desc[i].src_bytes, 0), cap + B2G_MAX_OVERHEAD) / 2 + 2;
   }
   itab_cap = std::min<int64_t>(itab_cap, (int64_t)1 << 27);
-  if (!g_two_phase) itab_cap = rec_cap = 0;
+  if (!c->two_phase) itab_cap = rec_cap = 0;
   if (int rc = L.d_itab.ensure(sizeof(ItemRec) * (size_t)itab_cap + 16)) return rc;
   if (int rc = L.d_rec.ensure(sizeof(uint2) * (size_t)rec_cap + 16)) return rc;
   CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
@@ -283,20 +302,24 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   }
   CU(cudaEventRecord(L.ev[2], s));
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(L.h_res.p, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(h_res, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(L.res_ready, s));
   return 0;
 }
 
-int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s) {
+// ci / base: pinned plan arrays of n / n + 1 entries (nullptr: the lane's own); h_res: where the results land
+int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s,
+                     CInfo* ci = nullptr, int32_t* base = nullptr, DResult* h_res = nullptr) {
   const b2g_params& p = c->p;
   if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
   if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
   if (p.clevel > 9) return B2G_ERR_CODEC_PARAM;
-  if (int rc = L.h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
-  if (int rc = L.h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
-  CInfo* ci = (CInfo*)L.h_cinfo.p;
-  int32_t* base = (int32_t*)L.h_base.p;
+  if (!ci) {
+    if (int rc = L.h_cinfo.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+    if (int rc = L.h_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
+    ci = (CInfo*)L.h_cinfo.p;
+    base = (int32_t*)L.h_base.p;
+  }
   int64_t items = 0;
   int max_stream = 1;
   CParams cp;
@@ -321,7 +344,10 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
   if (int rc = L.d_base.ensure(sizeof(int32_t) * ((size_t)n + 1))) return rc;
   if (int rc = L.d_ctl.ensure(sizeof(BatchCtl) * 2)) return rc;
-  if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (!h_res) {
+    if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
+    h_res = (DResult*)L.h_res.p;
+  }
   CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaMemcpyAsync(L.d_cinfo.p, ci, sizeof(CInfo) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaMemcpyAsync(L.d_base.p, base, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
@@ -374,7 +400,7 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   c->launches++;
   CU(cudaEventRecord(L.ev[2], s));
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(L.h_res.p, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(h_res, L.d_res.p, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(L.res_ready, s));
   return 0;
 }
@@ -393,7 +419,12 @@ int finish(b2g_ctx* c, Lane& L, b2g_chunk* chunks, int n) {
   if (timing) {  // developer switch: the parse / replay split of a decode batch
     float m = 0;
     if (cudaEventElapsedTime(&m, L.ev[1], L.ev_mid) == cudaSuccess && m > 0)
-      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms\n", a, m, b - m);
+    {
+      BatchCtl ctl[2];
+      cudaMemcpy(ctl, L.d_ctl.p, sizeof(ctl), cudaMemcpyDeviceToHost);
+      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms; items %d, replayed %d\n", a, m, b - m,
+              ctl[0].total_items, ctl[0].replayed);
+    }
   }
   return 0;
 }
@@ -416,6 +447,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
   }
   b2g_ctx* c = new b2g_ctx();
   c->p = *params;
+  c->two_phase = env_two_phase();
   if (c->p.typesize == 0) c->p.typesize = 1;
   if (c->p.blocksize <= 0) c->p.blocksize = 32768;
   int dev = params->device;
@@ -443,6 +475,9 @@ void b2g_destroy(b2g_ctx* c) {
   for (Lane& L : c->lanes) L.release();
   c->d_in.release();
   c->d_out.release();
+  for (HostBuf* b : {&c->h_desc_all, &c->h_res_all, &c->h_cinfo_all, &c->h_base_all}) b->release();
+  for (cudaEvent_t e : c->sub_done) cudaEventDestroy(e);
+  if (c->d2h_stream) { cudaStreamSynchronize(c->d2h_stream); cudaStreamDestroy(c->d2h_stream); }
   delete c;
 }
 
@@ -492,10 +527,13 @@ int b2g_compress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_s
   return rc;
 }
 
+static int wait_host_batch(b2g_ctx* c);
+
 int b2g_wait(b2g_ctx* c) {
   if (!c) return B2G_ERR_INVALID_PARAM;
   if (!c->pend) return 0;
   if (int rc = use_device(c)) return rc;
+  if (c->pend_kind != 0) return wait_host_batch(c);
   b2g_chunk* chunks = c->pend;
   int n = c->pend_n;
   c->pend = nullptr;
@@ -540,12 +578,27 @@ static std::vector<int> split_batch(const std::vector<size_t>& payload) {
   return bounds;
 }
 
-int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+// ---- host-pointer batches ------------------------------------------------------------------------------------------
+// Everything that does not depend on a device result is enqueued up front: per sub-batch the H2D copies, the kernels and
+// the copy of the per-chunk results, on the lane streams in rotation.  Decompress also enqueues its D2H copies (the sizes
+// are in the headers); compress copies a chunk back once its size is known, from b2g_wait(), on a stream of its own so
+// that those copies never queue behind the H2D copies of later sub-batches.
+static int ensure_sub_events(b2g_ctx* c, int nsub) {
+  while ((int)c->sub_done.size() < nsub) {
+    cudaEvent_t e = nullptr;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->sub_done.push_back(e);
+  }
+  if (!c->d2h_stream) CU(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+  return 0;
+}
+
+int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
   if (n == 0) return 0;
   if (int rc = use_device(c)) return rc;
-  (void)cuda_stream;  // the call returns when the data is back in host memory; it runs on the context's own lanes
+  (void)cuda_stream;  // host-pointer batches run on the context's own lane streams
   std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n), payload(n);
   size_t in_total = 0, out_total = 0;
   int maxblock = 0, maxstream = 0;
@@ -574,25 +627,43 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
     out_off[i] = out_total; out_len[i] = give; out_total += align_up(give + 8, 256);
     payload[i] = take + give;
   }
+  // Process the batch in the order of the destination addresses: outputs that are neighbours in host memory (the chunks
+  // of a channel decoded into one array) become neighbours in d_out and go back with ONE copy per sub-batch.
+  std::vector<int>& ord = c->pend_order;
+  ord.resize(n);
+  for (int i = 0; i < n; i++) ord[i] = i;
+  std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return (uintptr_t)chunks[a].dst < (uintptr_t)chunks[b].dst; });
+  in_total = out_total = 0;
+  std::vector<size_t> pay(n);
+  for (int k = 0; k < n; k++) {
+    const int i = ord[k];
+    in_off[i] = in_total; in_total += align_up(in_len[i] + 8, 256);
+    const int p = k ? ord[k - 1] : -1;
+    if (p >= 0 && out_len[p] && out_len[i] && (const uint8_t*)chunks[p].dst + out_len[p] == (const uint8_t*)chunks[i].dst)
+      out_off[i] = out_off[p] + out_len[p];
+    else
+      out_off[i] = align_up(out_total, 256);
+    out_total = out_off[i] + out_len[i] + 8;
+    pay[k] = payload[i];
+  }
   if (int rc = set_geometry(c, std::max(maxblock, c->blocksize))) return rc;
   if (int rc = c->d_in.ensure(in_total + 256)) return rc;
-  if (int rc = c->d_out.ensure(out_total + 256)) return rc;
+  if (int rc = c->d_out.ensure(out_total + 512)) return rc;
+  if (int rc = c->h_desc_all.ensure(sizeof(DChunk) * (size_t)n)) return rc;
+  if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
   c->last_ms[0] = c->last_ms[1] = 0;
-  const std::vector<int> bounds = split_batch(payload);
-  const int nsub = (int)bounds.size() - 1;
-  for (int k = 0; k < nsub + kLanes; k++) {
-    Lane& L = c->lanes[k % kLanes];
-    if (k >= kLanes) {  // retire the sub-batch that used this lane last
-      const int lo = bounds[k - kLanes], cnt = bounds[k - kLanes + 1] - lo;
-      if (int rc = finish(c, L, chunks + lo, cnt)) return rc;
-    }
-    if (k >= nsub) continue;
-    const int lo = bounds[k], cnt = bounds[k + 1] - lo;
+  c->pend_bounds = split_batch(pay);
+  const int nsub = (int)c->pend_bounds.size() - 1;
+  if (int rc = ensure_sub_events(c, nsub)) return rc;
+  DChunk* desc = (DChunk*)c->h_desc_all.p;
+  DResult* res = (DResult*)c->h_res_all.p;
+  for (int k = 0; k < nsub; k++) {
+    Lane& L = c->lanes[k % g_lanes];
+    const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
     cudaStream_t s = L.stream;
-    if (int rc = L.h_chunks.ensure(sizeof(DChunk) * (size_t)cnt)) return rc;
-    DChunk* h = (DChunk*)L.h_chunks.p;
-    for (int i = lo; i < lo + cnt; i++) {
-      DChunk& d = h[i - lo];
+    for (int q = lo; q < lo + cnt; q++) {
+      const int i = ord[q];
+      DChunk& d = desc[q];
       d.src = (const uint8_t*)c->d_in.p + in_off[i];
       d.dst = (uint8_t*)c->d_out.p + out_off[i];
       d.src_bytes = chunks[i].src_bytes == INT32_MAX ? (int32_t)in_len[i]
@@ -600,64 +671,136 @@ int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream
       d.dst_cap = chunks[i].dst_capacity;
       if (in_len[i]) CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
     }
-    if (int rc = enqueue_decode(c, L, h, cnt, s, any_zstd, std::max(maxstream, 1))) return rc;
-    for (int i = lo; i < lo + cnt; i++)
-      if (out_len[i]) CU(cudaMemcpyAsync(chunks[i].dst, h[i - lo].dst, out_len[i], cudaMemcpyDeviceToHost, s));
+    if (int rc = enqueue_decode(c, L, desc + lo, cnt, s, any_zstd, std::max(maxstream, 1), res + lo)) return rc;
+    for (int q = lo; q < lo + cnt;) {  // one copy per run of neighbouring outputs
+      const int i = ord[q];
+      size_t len = out_len[i];
+      int e = q + 1;
+      while (e < lo + cnt && out_len[ord[e]] && len && out_off[ord[e]] == out_off[i] + len &&
+             (uint8_t*)chunks[ord[e]].dst == (uint8_t*)chunks[i].dst + len) {
+        len += out_len[ord[e]];
+        e++;
+      }
+      if (len) CU(cudaMemcpyAsync(chunks[i].dst, desc[q].dst, len, cudaMemcpyDeviceToHost, s));
+      q = e;
+    }
+    CU(cudaEventRecord(c->sub_done[k], s));
   }
-  for (Lane& L : c->lanes) CU(cudaStreamSynchronize(L.stream));
+  c->pend = chunks; c->pend_n = n; c->pend_kind = 1;
   return 0;
 }
 
-int b2g_compress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
   if (n == 0) return 0;
   if (int rc = use_device(c)) return rc;
   (void)cuda_stream;
-  std::vector<size_t> in_off(n), out_off(n), payload(n);
+  // Process the batch in the order of the source addresses: raw chunks that are neighbours in host memory (a channel
+  // handed over as one array) become neighbours in d_in and are uploaded with ONE copy per sub-batch.
+  std::vector<int>& ord = c->pend_order;
+  ord.resize(n);
+  for (int i = 0; i < n; i++) ord[i] = i;
+  std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return (uintptr_t)chunks[a].src < (uintptr_t)chunks[b].src; });
+  std::vector<size_t> in_off(n), payload(n);
+  c->pend_out_off.assign(n, 0);
   size_t in_total = 0, out_total = 0;
-  for (int i = 0; i < n; i++) {
-    const int32_t sz = std::max(chunks[i].src_bytes, 0);
-    const int32_t cap = std::max(std::min(chunks[i].dst_capacity, sz + B2G_MAX_OVERHEAD), 0);
-    in_off[i] = in_total; in_total += align_up((size_t)sz + 8, 256);
-    out_off[i] = out_total; out_total += align_up((size_t)cap + 8, 256);
-    payload[i] = (size_t)sz;
+  for (int k = 0; k < n; k++) {
+    const int i = ord[k];
+    const size_t sz = (size_t)std::max(chunks[i].src_bytes, 0);
+    const int32_t cap = std::max(std::min<int64_t>(chunks[i].dst_capacity, (int64_t)sz + B2G_MAX_OVERHEAD), (int64_t)0);
+    const int p = k ? ord[k - 1] : -1;
+    const size_t psz = p >= 0 ? (size_t)std::max(chunks[p].src_bytes, 0) : 0;
+    if (p >= 0 && psz && sz && (const uint8_t*)chunks[p].src + psz == (const uint8_t*)chunks[i].src)
+      in_off[i] = in_off[p] + psz;
+    else
+      in_off[i] = align_up(in_total, 256);
+    in_total = in_off[i] + sz + 8;
+    c->pend_out_off[i] = out_total; out_total += align_up((size_t)cap + 8, 256);
+    payload[k] = sz;
   }
-  if (int rc = c->d_in.ensure(in_total + 256)) return rc;
+  if (int rc = c->d_in.ensure(in_total + 512)) return rc;
   if (int rc = c->d_out.ensure(out_total + 256)) return rc;
+  c->pend_bounds = split_batch(payload);
+  const int nsub = (int)c->pend_bounds.size() - 1;
+  if (int rc = c->h_desc_all.ensure((sizeof(DChunk) + sizeof(int32_t)) * (size_t)n)) return rc;
+  if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
+  if (int rc = c->h_cinfo_all.ensure(sizeof(CInfo) * (size_t)n)) return rc;
+  if (int rc = c->h_base_all.ensure(sizeof(int32_t) * ((size_t)n + (size_t)nsub))) return rc;
+  if (int rc = ensure_sub_events(c, nsub)) return rc;
   c->last_ms[0] = c->last_ms[1] = 0;
-  const std::vector<int> bounds = split_batch(payload);
-  const int nsub = (int)bounds.size() - 1;
-  for (int k = 0; k < nsub + kLanes; k++) {
-    Lane& L = c->lanes[k % kLanes];
-    if (k >= kLanes) {  // retire: the sizes are needed before the chunks can be copied back
-      const int lo = bounds[k - kLanes], cnt = bounds[k - kLanes + 1] - lo;
-      if (int rc = finish(c, L, chunks + lo, cnt)) return rc;
-      for (int i = lo; i < lo + cnt; i++)
-        if (chunks[i].out_bytes > 0)
-          CU(cudaMemcpyAsync(chunks[i].dst, (uint8_t*)c->d_out.p + out_off[i], (size_t)chunks[i].out_bytes,
-                             cudaMemcpyDeviceToHost, L.stream));
-    }
-    if (k >= nsub) continue;
-    const int lo = bounds[k], cnt = bounds[k + 1] - lo;
+  DChunk* desc = (DChunk*)c->h_desc_all.p;
+  int32_t* nb = (int32_t*)(desc + n);
+  DResult* res = (DResult*)c->h_res_all.p;
+  CInfo* ci = (CInfo*)c->h_cinfo_all.p;
+  int32_t* base = (int32_t*)c->h_base_all.p;
+  for (int k = 0; k < nsub; k++) {
+    Lane& L = c->lanes[k % g_lanes];
+    const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
     cudaStream_t s = L.stream;
-    if (int rc = L.h_chunks.ensure((sizeof(DChunk) + sizeof(int32_t)) * (size_t)cnt)) return rc;
-    DChunk* h = (DChunk*)L.h_chunks.p;
-    int32_t* nb = (int32_t*)(h + cnt);
-    for (int i = lo; i < lo + cnt; i++) {
-      DChunk& d = h[i - lo];
+    for (int q = lo; q < lo + cnt; q++) {
+      const int i = ord[q];
+      DChunk& d = desc[q];
       d.src = (const uint8_t*)c->d_in.p + in_off[i];
-      d.dst = (uint8_t*)c->d_out.p + out_off[i];
+      d.dst = (uint8_t*)c->d_out.p + c->pend_out_off[i];
       d.src_bytes = chunks[i].src_bytes;
       d.dst_cap = std::min(chunks[i].dst_capacity, std::max(chunks[i].src_bytes, 0) + B2G_MAX_OVERHEAD);
-      nb[i - lo] = chunks[i].src_bytes;
-      if (chunks[i].src_bytes > 0)
-        CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, (size_t)chunks[i].src_bytes, cudaMemcpyHostToDevice, s));
+      nb[q] = chunks[i].src_bytes;
     }
-    if (int rc = enqueue_compress(c, L, h, nb, cnt, s)) return rc;
+    for (int q = lo; q < lo + cnt;) {  // one copy per run of neighbouring inputs
+      const int i = ord[q];
+      size_t len = (size_t)std::max(chunks[i].src_bytes, 0);
+      int e = q + 1;
+      while (e < lo + cnt && len && chunks[ord[e]].src_bytes > 0 && in_off[ord[e]] == in_off[i] + len &&
+             (const uint8_t*)chunks[ord[e]].src == (const uint8_t*)chunks[i].src + len) {
+        len += (size_t)chunks[ord[e]].src_bytes;
+        e++;
+      }
+      if (len) CU(cudaMemcpyAsync((void*)desc[q].src, chunks[i].src, len, cudaMemcpyHostToDevice, s));
+      q = e;
+    }
+    if (int rc = enqueue_compress(c, L, desc + lo, nb + lo, cnt, s, ci + lo, base + lo + k, res + lo)) return rc;
+    CU(cudaEventRecord(c->sub_done[k], s));
   }
-  for (Lane& L : c->lanes) CU(cudaStreamSynchronize(L.stream));
+  c->pend = chunks; c->pend_n = n; c->pend_kind = 2;
   return 0;
+}
+
+// Completes a host-pointer batch: per sub-batch, in order, the results; for compress the chunks are copied back as soon
+// as their sizes are known.
+static int wait_host_batch(b2g_ctx* c) {
+  b2g_chunk* chunks = c->pend;
+  const int kind = c->pend_kind;
+  c->pend = nullptr;
+  c->pend_kind = 0;
+  const int nsub = (int)c->pend_bounds.size() - 1;
+  const DResult* r = (const DResult*)c->h_res_all.p;
+  int rc_all = 0;
+  for (int k = 0; k < nsub; k++) {
+    if (cuda_fail(cudaEventSynchronize(c->sub_done[k]), "cudaEventSynchronize")) { rc_all = B2G_ERR_NO_DEVICE; break; }
+    for (int q = c->pend_bounds[k]; q < c->pend_bounds[k + 1]; q++) {
+      const int i = c->pend_order[q];
+      chunks[i].status = r[q].status;
+      chunks[i].out_bytes = r[q].status < 0 ? 0 : r[q].out_bytes;
+      if (kind == 2 && chunks[i].out_bytes > 0 &&
+          cuda_fail(cudaMemcpyAsync(chunks[i].dst, (uint8_t*)c->d_out.p + c->pend_out_off[i], (size_t)chunks[i].out_bytes,
+                                    cudaMemcpyDeviceToHost, c->d2h_stream), "cudaMemcpyAsync"))
+        rc_all = B2G_ERR_NO_DEVICE;
+    }
+  }
+  for (Lane& L : c->lanes) if (cuda_fail(cudaStreamSynchronize(L.stream), "cudaStreamSynchronize")) rc_all = B2G_ERR_NO_DEVICE;
+  if (c->d2h_stream && cuda_fail(cudaStreamSynchronize(c->d2h_stream), "cudaStreamSynchronize")) rc_all = B2G_ERR_NO_DEVICE;
+  return rc_all;
+}
+
+int b2g_decompress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (int rc = b2g_decompress_batch_async(c, chunks, n, cuda_stream)) return rc;
+  return b2g_wait(c);
+}
+
+int b2g_compress_batch(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if (int rc = b2g_compress_batch_async(c, chunks, n, cuda_stream)) return rc;
+  return b2g_wait(c);
 }
 
 int b2g_filter_device(b2g_ctx* c, int filter, int forward, int typesize, int format_version, const void* src,

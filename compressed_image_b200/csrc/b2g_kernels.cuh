@@ -171,6 +171,7 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
       a.ctl[k].total_items = run;
       a.ctl[k].ticket = 0;
       a.ctl[k].parse_ticket = 0;
+      a.ctl[k].replayed = 0;
       a.base[k * (a.n + 1) + a.n] = run;
     }
     long long run = 0;
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(kParseThreads) k_parse(DecodeArgs a) {
     ItemRec ir;
     ir.pos = 0; ir.csize = 0; ir.nseq = 0; ir.slack = 0;
     LaneParse L;
-    L.in = nullptr; L.rec = nullptr; L.n = 0; L.cap = 0; L.maxrec = 0;
+    L.in = nullptr; L.rec = nullptr; L.n = 0; L.cap = 0; L.maxrec = 0; L.slack = 0;
     bool active = false, lz4 = true;
     if (item < total) {
       const int c = find_chunk(a.base, a.n, item, 0);
@@ -317,10 +318,22 @@ __global__ void __launch_bounds__(kParseThreads) k_parse(DecodeArgs a) {
   }
 }
 
+// dst[0..n) = src[0..n) with dst in shared memory and dst = src (mod 16): the aligned body goes through asynchronous
+// 16-byte copies that are all in flight at once (a plain load / store loop pays the global latency once per 512 bytes).
+__device__ __forceinline__ void stage_payload(uint8_t* dst, const uint8_t* src, int n, int lane) {
+  int head = (int)((16 - ((uintptr_t)src & 15)) & 15);
+  if (head > n) head = n;
+  const int body = (n - head) >> 4;
+  for (int g = lane; g < body; g += 32) async_copy16(dst + head + 16 * g, src + head + 16 * g);
+  if (lane < head) dst[lane] = src[lane];
+  for (int i = head + (body << 4) + lane; i < n; i += 32) dst[i] = src[i];
+  async_copy_wait();
+}
+
 // One stream (blosc2.c:1783-1923) decoded by one warp into win[0..neblock).  `wbytes` = usable bytes of the window:
 // lz4 / blosclz streams are first copied to its top (16-byte loads, same alignment phase as the source) and decoded in
 // place, so the byte-serial part of the decoder only ever touches the window.
-template <bool Z, bool STAGE>
+template <bool Z, bool STAGE, bool SMEM>
 __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, int32_t csize, int32_t avail,
                                              uint8_t* win, int32_t wbytes, int32_t neblock, ZWork* zw) {
   const int lane = lane_id();
@@ -353,7 +366,8 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
       const int m = (int)((uintptr_t)payload & 15);
       const int a = ((wbytes - csize - m) & ~15) + m;  // a + csize <= wbytes, (win + a) = payload (mod 16)
       if (wbytes - csize - m >= 0) {
-        copy_bytes(win + a, payload, csize, lane, 32);
+        if (SMEM) stage_payload(win + a, payload, csize, lane);  // asynchronous 16-byte copies, all in flight at once
+        else copy_bytes(win + a, payload, csize, lane, 32);
         __syncwarp();
         got = fmt == kFmtLz4 ? lz4_decode_warp_t<true>(win + a, csize, win, neblock, a)
                              : blosclz_decode_warp_t<true>(win + a, csize, win, neblock, a);
@@ -412,7 +426,7 @@ __device__ __forceinline__ int decode_streams(const StreamJob& jb, uint8_t* win,
     if (cs < 0 && jb.srcsize - pos < 1) return kErrRead;
     if (k >= jb.s) {
       const int32_t o = jb.scatter ? 0 : k * jb.neblock;  // a plane has the window to itself
-      const int rc = decode_stream<Z, STAGE>(jb.fmt, jb.src + pos, cs, jb.srcsize - pos, win + o, wbytes - o,
+      const int rc = decode_stream<Z, STAGE, SMEM>(jb.fmt, jb.src + pos, cs, jb.srcsize - pos, win + o, wbytes - o,
                                              jb.neblock, zw);
       if (rc < 0) return rc;
     }
@@ -486,7 +500,7 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
         const int room = a.wcap - ir.csize - m;
         const int ao = (room & ~15) + m;  // ao + csize <= wcap, (win + ao) = payload (mod 16)
         if (room >= 0 && ir.slack <= ao && need <= a.wcap) {
-          copy_bytes(win_s + ao, payload, ir.csize, lane, 32);
+          stage_payload(win_s + ao, payload, ir.csize, lane);
           __syncwarp();
           const int got = seq_execute_warp(a.rec + d.rec_base + ir.pos / d.rec_div, ir.nseq, win_s, ao, ir.csize,
                                            neblock, (uint4*)(win_s + a.wcap));
@@ -496,6 +510,7 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
 #ifdef B2G_SIM
             if (lane == 0) sim_two_phase_hits()++;
 #endif
+            if (lane == 0) atomicAdd(&a.ctl->replayed, 1);
             done = true;
             err = 0;
           }

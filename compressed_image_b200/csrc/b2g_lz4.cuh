@@ -37,6 +37,13 @@ __device__ __forceinline__ void lz_literal_copy(uint8_t* out, int op, const uint
                                                 int lane) {
   if (!INPLACE || delta >= lit) {
     if (lit <= 32) { if (lane < lit) out[op + lane] = in[pos + lane]; }
+    else if (lit <= 64) {  // both loads in flight before the stores
+      const uint8_t v0 = in[pos + lane];
+      uint8_t v1 = 0;
+      if (lane + 32 < lit) v1 = in[pos + 32 + lane];
+      out[op + lane] = v0;
+      if (lane + 32 < lit) out[op + 32 + lane] = v1;
+    }
     else if (lit < 128) for (int i = lane; i < lit; i += 32) out[op + i] = in[pos + i];
     else copy_bytes(out + op, in + pos, lit, lane, 32);
   } else {

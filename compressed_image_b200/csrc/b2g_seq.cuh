@@ -66,7 +66,6 @@ struct LaneParse {
   int want;              // position the next piece must start at
   int lo, hi;            // payload positions [lo, hi) are staged at sm[p - lo]
   const uint8_t* sm;     // this lane's piece (shared memory)
-  int ntok, ntok_pos;    // lz4: the next token, already seen in the offset's 4-byte window (-1: not seen)
 };
 
 __device__ __forceinline__ uint32_t pc_byte(const LaneParse& L, int p) {
@@ -106,61 +105,82 @@ __device__ __forceinline__ int pc_varlen(const LaneParse& L, int& pos, int ilimi
   return pos <= ilimit ? kStepGo : kStepFail;
 }
 
-// One half-sequence of an LZ4 block.  Mirrors lz4_decode_warp_t check for check.
-__device__ __forceinline__ int lz4_parse_step(LaneParse& L) {
-  if (L.phase == 0) {
-    const int ip = L.ip;
-    if (ip >= L.n || L.nrec >= L.maxrec) return kStepFail;
-    L.want = ip;
-    uint32_t tok;
-    if (L.ntok_pos == ip) {
-      tok = (uint32_t)L.ntok;  // seen in the previous sequence's offset window
-    } else {
-      if (ip >= L.hi) return kStepRefill;
-      tok = pc_byte(L, ip);
+// The LZ4 token chain of one lane, as far as its piece reaches.  Mirrors lz4_decode_warp_t check for check.  The common
+// sequence costs ONE shared-memory access: the 4-byte window at the offset also holds the first match-length extension
+// byte or the next token and its first literal-length extension byte.  Returns kStepRefill / kStepDone / kStepFail.
+__device__ __forceinline__ int lz4_parse_run(LaneParse& L) {
+  const int n = L.n, cap = L.cap, hi = L.hi, maxrec = L.maxrec;
+  int ip = L.ip, op = L.op, nrec = L.nrec, slack = L.slack;
+  int lit = L.lit, pos = L.pos, mlc = L.mlc;
+  int tokc = -1, b1 = -1;  // next token / the byte after it, when already seen (-1: not)
+  int ret;
+  if (L.phase == 1) goto second_half;
+  for (;;) {
+    if (ip >= n || nrec >= maxrec) { ret = kStepFail; break; }
+    if (tokc < 0) {
+      if (ip >= hi) { L.phase = 0; L.want = ip; ret = kStepRefill; break; }
+      tokc = (int)pc_byte(L, ip);
+      b1 = -1;
     }
-    int lit = (int)(tok >> 4);
-    int pos = ip + 1;
+    lit = tokc >> 4;
+    mlc = tokc & 15;
+    pos = ip + 1;
     if (lit == 15) {
-      if (pos >= L.n - 15) return kStepFail;
-      const int r = pc_varlen(L, pos, L.n - 15, lit);
-      if (r != kStepGo) return r;
+      if (pos >= n - 15) { ret = kStepFail; break; }
+      if (b1 >= 0 && b1 != 255) {
+        lit += b1;  // pos + 1 <= n - 15 holds
+        pos++;
+      } else {
+        const int r = pc_varlen(L, pos, n - 15, lit);
+        if (r == kStepRefill) { L.phase = 0; L.want = ip; ret = r; break; }  // the token is read again
+        if (r != kStepGo) { ret = r; break; }
+      }
     }
-    const int cpy = L.op + lit;
-    if (cpy > L.cap - 12 || pos + lit > L.n - 8) {  // last sequence: literals only, consuming the input exactly
-      if (pos + lit != L.n || cpy > L.cap) return kStepFail;
-      L.rec[L.nrec++] = seq_pack(lit, 0, 0, pos);
-      L.op = cpy;
-      return kStepDone;
+    if (op + lit > cap - 12 || pos + lit > n - 8) {  // last sequence: literals only, consuming the input exactly
+      if (pos + lit != n || op + lit > cap) { ret = kStepFail; break; }
+      L.rec[nrec++] = seq_pack(lit, 0, 0, pos);
+      op += lit;
+      ret = kStepDone;
+      break;
     }
-    L.lit = lit; L.pos = pos; L.mlc = (int)(tok & 15u); L.phase = 1;
+  second_half:
+    {
+      const int opos = pos + lit;  // <= n - 8: offset, then a match-length extension or the next token
+      if (opos + 4 > hi) { L.phase = 1; L.want = opos; ret = kStepRefill; break; }
+      const uint32_t w = pc_word(L, opos);
+      const int offset = (int)(w & 0xffffu);
+      int ipn = opos + 2;
+      int ml = mlc;
+      if (ml == 15) {
+        const int e = (int)((w >> 16) & 0xffu);
+        if (e != 255) {
+          ml += e;  // ipn + 1 <= n - 4 holds
+          ipn++;
+          tokc = (int)(w >> 24);
+          b1 = -1;
+        } else {
+          const int r = pc_varlen(L, ipn, n - 4, ml);
+          if (r == kStepRefill) { L.phase = 1; L.want = opos; ret = r; break; }
+          if (r != kStepGo) { ret = r; break; }
+          tokc = -1;
+        }
+      } else {
+        tokc = (int)((w >> 16) & 0xffu);
+        b1 = (int)(w >> 24);
+      }
+      ml += 4;
+      const int cpy = op + lit;
+      if (offset > cpy) { ret = kStepFail; break; }  // offset 0 is accepted (zeros), as in lz4_decode_warp_t
+      const int mend = cpy + ml;
+      if (mend > cap - 5) { ret = kStepFail; break; }  // lz4.c:2419-2423: the last 5 bytes are always literals
+      L.rec[nrec++] = seq_pack(lit, ml, offset, pos);
+      slack = max(slack, mend - ipn);
+      op = mend;
+      ip = ipn;
+    }
   }
-  {
-    const int opos = L.pos + L.lit;  // <= n - 8
-    L.want = opos;
-    if (opos + 4 > L.hi) return kStepRefill;  // opos + 4 <= n - 4: offset, the next token and one more byte
-    const uint32_t w = pc_word(L, opos);
-    const int offset = (int)(w & 0xffffu);
-    int ipn = opos + 2;
-    L.ntok = (int)((w >> 16) & 0xffu);
-    L.ntok_pos = ipn;  // wrong when a match-length extension follows: ipn moves on and the compare fails
-    int ml = L.mlc;
-    if (ml == 15) {
-      const int r = pc_varlen(L, ipn, L.n - 4, ml);
-      if (r != kStepGo) return r;
-    }
-    ml += 4;
-    const int cpy = L.op + L.lit;
-    if (offset > cpy) return kStepFail;  // offset 0 is accepted (zeros), as in lz4_decode_warp_t
-    const int mend = cpy + ml;
-    if (mend > L.cap - 5) return kStepFail;  // lz4.c:2419-2423: the last 5 bytes are always literals
-    L.rec[L.nrec++] = seq_pack(L.lit, ml, offset, L.pos);
-    L.slack = max(L.slack, mend - ipn);
-    L.op = mend;
-    L.ip = ipn;
-    L.phase = 0;
-  }
-  return kStepGo;
+  L.ip = ip; L.op = op; L.nrec = nrec; L.slack = slack; L.lit = lit; L.pos = pos; L.mlc = mlc;
+  return ret;
 }
 
 // One control byte of a blosclz stream (L.ip = position of the control byte; the first one is masked by the caller via
@@ -226,7 +246,7 @@ __device__ __forceinline__ int blosclz_parse_step(LaneParse& L) {
 __device__ __forceinline__ int seq_parse_warp(LaneParse& L, bool active, bool lz4, uint8_t* sm) {
   const int lane = lane_id();
   L.ip = 0; L.op = 0; L.nrec = 0; L.slack = 0; L.phase = 0; L.plit = 0; L.ppos = 0; L.want = 0; L.lo = 0; L.hi = 0;
-  L.ntok = 0; L.ntok_pos = -1;
+  L.lit = 0; L.pos = 0; L.mlc = 0;
   L.sm = sm + lane * kPieceBytes;
   int state = (active && L.n > 0 && (!lz4 || L.cap > 0)) ? kStepRefill : kStepFail;
   int stuck = -1;  // position of the last refill request: asking for the same piece twice means it can never suffice
@@ -253,7 +273,7 @@ __device__ __forceinline__ int seq_parse_warp(LaneParse& L, bool active, bool lz
     }
     __syncwarp();
     if (state == kStepGo) {
-      if (lz4) { do { state = lz4_parse_step(L); } while (state == kStepGo); }
+      if (lz4) state = lz4_parse_run(L);
       else { do { state = blosclz_parse_step(L); } while (state == kStepGo); }
     }
     __syncwarp();
@@ -301,15 +321,16 @@ __device__ __forceinline__ int seq_execute_warp(const uint2* rec, int nseq, uint
     const int cnt = min(32, nseq - g);
     // ---- literal runs of the whole group: independent of every match ------------------------------------------
     for (int k0 = 0; k0 < cnt; k0 += 8) {
-      uint8_t v[8];
+      uint8_t v0[8], v1[8];  // a lane carries bytes `lane` and `32 + lane` of each run: runs of up to 64 bytes
       bool longrun = false;
 #pragma unroll
       for (int u = 0; u < 8; u++) {
         const uint4 q = sq[k0 + u];  // lanes past the last record hold zero records
         const int L = (int)(q.x & 0xffffu);
-        v[u] = 0;
-        if (lane < L) v[u] = win[q.y + lane];
-        longrun |= L > 32;
+        v0[u] = 0; v1[u] = 0;
+        if (lane < L) v0[u] = win[q.y + lane];
+        if (lane + 32 < L) v1[u] = win[q.y + 32 + lane];
+        longrun |= L > 64;
       }
       __syncwarp();  // in place, a run's destination may overlap the source of an earlier run of this batch
       if (!longrun) {
@@ -317,10 +338,11 @@ __device__ __forceinline__ int seq_execute_warp(const uint2* rec, int nseq, uint
         for (int u = 0; u < 8; u++) {
           const uint4 q = sq[k0 + u];
           const int L = (int)(q.x & 0xffffu);
-          if (lane < L) win[q.z + lane] = v[u];
+          if (lane < L) win[q.z + lane] = v0[u];
+          if (lane + 32 < L) win[q.z + 32 + lane] = v1[u];
         }
       } else {
-        // A run longer than 32 bytes: its tail is still unread, and in place the destinations of the LATER runs of this
+        // A run longer than 64 bytes: its tail is still unread, and in place the destinations of the LATER runs of this
         // batch may lie on it.  Copy the batch run by run instead, each a forward memmove in 32-byte steps (a run's
         // destination never reaches the source of a later run, and never passes its own source).
         for (int u = 0; u < 8; u++) {

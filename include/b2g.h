@@ -108,6 +108,15 @@ B2G_API int b2g_compress_batch(b2g_ctx* ctx, b2g_chunk* chunks, int n, void* cud
  * blocksize come from each chunk's own header.  HOST pointers. */
 B2G_API int b2g_decompress_batch(b2g_ctx* ctx, b2g_chunk* chunks, int n, void* cuda_stream);
 
+/* Asynchronous forms of the two host-pointer calls (no reference equivalent: blosc2 contexts are synchronous).  The
+ * call returns as soon as the H2D copies, the kernels and -- for decompress -- the D2H copies are enqueued on the
+ * context's own streams; b2g_wait() completes the batch (compress: copies each chunk back once its size is known) and
+ * fills out_bytes/status.  `chunks` and every src/dst buffer must stay valid until then; pinned host memory keeps the
+ * copies asynchronous.  One batch may be in flight per context: a decompress batch on one context and a compress batch
+ * on another use the PCIe link in both directions at once.  b2g_X_batch(...) == b2g_X_batch_async(...) + b2g_wait(). */
+B2G_API int b2g_compress_batch_async(b2g_ctx* ctx, b2g_chunk* chunks, int n, void* cuda_stream);
+B2G_API int b2g_decompress_batch_async(b2g_ctx* ctx, b2g_chunk* chunks, int n, void* cuda_stream);
+
 /* Device-resident variants: src/dst are DEVICE pointers on the context's device.  The work is enqueued on the
  * stream and the call returns without waiting; out_bytes/status of `chunks` are filled by b2g_wait(), until
  * which `chunks` must stay alive.  One batch may be in flight per context. */

@@ -237,3 +237,36 @@ def test_unsupported_encoders_fail_loudly():
         with pytest.raises(_b2g.B2GError) as e:
             g.compress_batch([src], codec, 5, 1, _data.SHUFFLE, 32768)
         assert e.value.code == -7
+
+
+def test_async_host_batches_on_two_contexts():
+    """b2g_decompress_batch_async on one context and b2g_compress_batch_async on another, in flight together, give what
+    the synchronous calls give; many sub-batches (B2G_SUBBATCH_MB is 32 by default, the batch is ~100 MB); a second
+    batch on a busy context is refused."""
+    from compressed_image_b200 import _b2g
+    g = _gpu()
+    kinds = ("half", "sensor", "text", "zeros", "random", "half") * 4
+    srcs = [_data.make_data(k, 4000000 + 4096 * i, 2, seed=i) for i, k in enumerate(kinds)]
+    ref_chunks = [c for _, c in g.compress_batch(srcs, _data.LZ4, 9, 2, _data.SHUFFLE, 32768)]
+    n = len(srcs)
+    with _b2g.Context(_data.LZ4, 9, 2, _data.SHUFFLE, 32768) as cd, _b2g.Context(_data.LZ4, 9, 2, _data.SHUFFLE, 32768) as cc:
+        outs = [np.full(s.size + 64, 0xAB, np.uint8) for s in srcs]
+        dsts = [np.full(s.size + 32 + 64, 0xAB, np.uint8) for s in srcs]
+        bd = cd.make_batch([c.ctypes.data for c in ref_chunks], [o.ctypes.data for o in outs],
+                           [int(c.size) for c in ref_chunks], [int(s.size) for s in srcs])
+        bc = cc.make_batch([s.ctypes.data for s in srcs], [d.ctypes.data for d in dsts], [int(s.size) for s in srcs],
+                           [int(s.size) + 32 for s in srcs])
+        for _ in range(2):
+            cd.decompress_batch_async(bd)
+            cc.compress_batch_async(bc)
+            with pytest.raises(_b2g.B2GError):
+                cd.decompress_batch_async(bd)
+            cc.wait()
+            cd.wait()
+            for i in range(n):
+                assert bd[i].status == 0 and bd[i].out_bytes == srcs[i].size
+                assert np.array_equal(outs[i][:srcs[i].size], srcs[i]) and np.all(outs[i][srcs[i].size:] == 0xAB)
+                assert bc[i].status == 0 and bc[i].out_bytes == ref_chunks[i].size
+                assert np.array_equal(dsts[i][:bc[i].out_bytes], ref_chunks[i])
+                assert np.all(dsts[i][srcs[i].size + 32:] == 0xAB)
+        cd.wait()   # nothing in flight: a no-op
