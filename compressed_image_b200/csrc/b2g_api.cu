@@ -85,10 +85,10 @@ struct Lane {
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
   cudaEvent_t ev_mid = nullptr;                      // between k_parse and k_decode (B2G_TIMING=1)
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_itab, d_rec;
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_itab, d_rec, d_stage, d_pair;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
   void release() {
-    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_itab, &d_rec}) b->release();
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_itab, &d_rec, &d_stage, &d_pair}) b->release();
     for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     if (res_ready) cudaEventDestroy(res_ready);
@@ -110,6 +110,7 @@ struct b2g_ctx {
   int max_grid_warps = 0;  // most worker warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
   bool two_phase = false;  // B2G_TWO_PHASE=1 at creation
+  bool pair_planes = true; // B2G_PAIR_PLANES=0 at creation: every plane scatters its own bytes
   // device + pinned work buffers
   DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
   // in-flight batch (device-resident API, or an asynchronous host-pointer batch)
@@ -253,6 +254,17 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     rec_cap += std::min<int64_t>(std::max(h_desc[i].src_bytes, 0), cap + B2G_MAX_OVERHEAD) / 2 + 2;
   }
   itab_cap = std::min<int64_t>(itab_cap, (int64_t)1 << 27);
+  // plane pairing (DecodeArgs::stage): a ring of staging slots, one flag per slot, a mailbox and a counter per item for
+  // each of the two kernels; everything but the slots is zeroed per batch
+  const int64_t pair_cap = c->pair_planes ? std::min<int64_t>(itab_cap, (int64_t)1 << 24) : 0;
+  const int nslots = 2048;
+  const size_t slot_bytes = (size_t)g.wcap;
+  const size_t pair_ints = (size_t)nslots + 4 * (size_t)pair_cap;
+  if (pair_cap > 0) {
+    if (int rc = L.d_stage.ensure((size_t)nslots * slot_bytes)) return rc;
+    if (int rc = L.d_pair.ensure(sizeof(int32_t) * pair_ints)) return rc;
+    CU(cudaMemsetAsync(L.d_pair.p, 0, sizeof(int32_t) * pair_ints, s));
+  }
   if (!c->two_phase) itab_cap = rec_cap = 0;
   if (int rc = L.d_itab.ensure(sizeof(ItemRec) * (size_t)itab_cap + 16)) return rc;
   if (int rc = L.d_rec.ensure(sizeof(uint2) * (size_t)rec_cap + 16)) return rc;
@@ -285,6 +297,13 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.itab = itab_cap > 0 ? (ItemRec*)L.d_itab.p : nullptr;
   da.itab_cap = (int32_t)itab_cap;
   da.rec = (uint2*)L.d_rec.p;
+  da.stage = pair_cap > 0 ? (uint8_t*)L.d_stage.p : nullptr;
+  da.slotflag = (int32_t*)L.d_pair.p;
+  da.mail = da.slotflag + nslots;
+  da.blkcnt = da.mail + 2 * pair_cap;
+  da.nslots = nslots;
+  da.slot_bytes = (int32_t)slot_bytes;
+  da.pair_cap = (int32_t)pair_cap;
   if (itab_cap > 0) {
     k_parse<<<c->sms * 6, kParseThreads, kParseSmemBytes, s>>>(da);
     c->launches++;
@@ -297,6 +316,8 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     da.ctl = pa.ctl + 1;
     da.wcap = gz.wcap;
     da.wstride = gz.wstride;
+    da.mail += pair_cap;     // the zstd class numbers its items from 0 again
+    da.blkcnt += pair_cap;
     k_decode<true><<<gz.grid, 32 * gz.warps, gz.smem, s>>>(da);
     c->launches++;
   }
@@ -422,8 +443,8 @@ int finish(b2g_ctx* c, Lane& L, b2g_chunk* chunks, int n) {
     {
       BatchCtl ctl[2];
       cudaMemcpy(ctl, L.d_ctl.p, sizeof(ctl), cudaMemcpyDeviceToHost);
-      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms; items %d, replayed %d\n", a, m, b - m,
-              ctl[0].total_items, ctl[0].replayed);
+      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms; items %d, replayed %d, blocks paired %d\n",
+              a, m, b - m, ctl[0].total_items, ctl[0].replayed, ctl[0].paired);
     }
   }
   return 0;
@@ -448,6 +469,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
   b2g_ctx* c = new b2g_ctx();
   c->p = *params;
   c->two_phase = env_two_phase();
+  { const char* e = getenv("B2G_PAIR_PLANES"); c->pair_planes = !(e && e[0] == '0'); }
   if (c->p.typesize == 0) c->p.typesize = 1;
   if (c->p.blocksize <= 0) c->p.blocksize = 32768;
   int dev = params->device;

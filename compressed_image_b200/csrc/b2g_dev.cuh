@@ -86,7 +86,10 @@ struct BatchCtl {
   int32_t total_items;   // written by the plan kernel (decode) or the host (compress)
   int32_t ticket;        // dynamic work distribution
   int32_t parse_ticket;  // k_parse's own ticket (32 items per draw)
-  int32_t replayed;      // items decoded by record replay (statistics: b2g_last_kernel_ms / B2G_TIMING)
+  int32_t replayed;      // items decoded by record replay (statistics: B2G_TIMING)
+  int32_t ring;          // plane staging: next slot to try (k_decode)
+  int32_t paired;        // blocks written out interleaved from staged planes (statistics)
+  int32_t pad2[2];
 };
 
 __device__ __forceinline__ int32_t ld_le32(const uint8_t* p) {

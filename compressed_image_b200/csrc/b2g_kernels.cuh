@@ -172,6 +172,8 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
       a.ctl[k].ticket = 0;
       a.ctl[k].parse_ticket = 0;
       a.ctl[k].replayed = 0;
+      a.ctl[k].ring = 0;
+      a.ctl[k].paired = 0;
       a.base[k * (a.n + 1) + a.n] = run;
     }
     long long run = 0;
@@ -232,6 +234,15 @@ struct DecodeArgs {
   ItemRec* itab;         // [itab_cap] per work item: what k_parse found (class 0 only; nullptr = one-pass decode only)
   int32_t itab_cap;
   uint2* rec;            // sequence records (regions: DInfo::rec_base)
+  // Plane pairing: the byte planes of a split block are decoded by different warps at different times.  Instead of each
+  // scattering its bytes into the raw block (partial sectors, read-modify-write in L2 / HBM), the planes that finish
+  // first are parked in an L2-resident ring of staging slots and the LAST plane's warp writes the whole block
+  // interleaved with 128-bit stores.  nullptr = off.
+  uint8_t* stage;        // [nslots][slot_bytes]
+  int32_t* slotflag;     // [nslots] 0 free, 1 in use
+  int32_t* mail;         // [pair_cap] per item: 0 nothing yet, slot + 1 = parked there, -1 = scattered directly
+  int32_t* blkcnt;       // [pair_cap] per block (index = its first item): planes finished
+  int32_t nslots, slot_bytes, pair_cap;
 };
 
 // Window bytes needed to decode a stream of `neblock` bytes with its compressed bytes staged in place above the output.
@@ -387,33 +398,165 @@ struct StreamJob {
   const uint8_t* src;   // the chunk
   uint8_t* raw;         // the raw block
   int32_t srcsize, first, s, s_end, ns, neblock, bsize;
+  int32_t item;         // the work item (batch-wide numbering)
   bool scatter;
   uint8_t fmt, filter, typesize, version;
 };
 
-// The decoded stream(s) of a work item, from the window into the raw block: a byte plane is scattered (the unshuffle
-// restricted to one plane, shuffle-generic.h:62-81), a whole block is un(bit)shuffled (pipeline_backward).
-__device__ __forceinline__ void unfilter_streams(const StreamJob& jb, const uint8_t* win) {
+// raw[i * ns + s] = plane[i]: the unshuffle restricted to one plane (shuffle-generic.h:62-81), byte stores.
+__device__ __forceinline__ void scatter_plane(uint8_t* raw, int ns, int s, const uint8_t* plane, int neblock, int lane) {
+  uint8_t* o = raw + s;
+  int i = lane;
+  for (; i + 7 * 32 < neblock; i += 8 * 32) {  // 8 loads in flight, then 8 stores
+    uint8_t v[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) v[u] = plane[i + 32 * u];
+#pragma unroll
+    for (int u = 0; u < 8; u++) o[(size_t)(i + 32 * u) * ns] = v[u];
+  }
+  for (; i < neblock; i += 32) o[(size_t)i * ns] = plane[i];
+}
+
+__device__ __forceinline__ int32_t mail_read(int32_t* p) {
+#ifdef B2G_SIM
+  return *(volatile int32_t*)p;
+#else
+  int32_t v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+#endif
+}
+
+// A decoded byte plane (win[0..neblock), plane jb.s of jb.ns) on its way into the raw block, see DecodeArgs::stage.
+__device__ __forceinline__ void pair_planes(const DecodeArgs& a, const StreamJob& jb, const uint8_t* win) {
+  const int lane = lane_id();
+  const int ns = jb.ns, s = jb.s, neblock = jb.neblock;
+  const int first = jb.item - s;  // the block's first item names the block
+  int old = 0;
+  __syncwarp();
+  if (lane == 0) old = atomicAdd(&a.blkcnt[first], 1);
+  old = __shfl_sync(kFull, old, 0);
+  if (old < ns - 1) {
+    // not the last plane of the block: park it
+    int slot = -1;
+    if (lane == 0) {
+      const int t = (int)((unsigned)atomicAdd(&a.ctl->ring, 1) % (unsigned)a.nslots);
+      if (atomicCAS(&a.slotflag[t], 0, 1) == 0) slot = t;
+    }
+    slot = __shfl_sync(kFull, slot, 0);
+    if (slot >= 0) {
+      uint4* d4 = (uint4*)(a.stage + (size_t)slot * (size_t)a.slot_bytes);
+      const uint4* s4 = (const uint4*)win;
+      for (int g = lane; g < (neblock >> 4); g += 32) d4[g] = s4[g];
+    } else {
+      scatter_plane(jb.raw, ns, s, win, neblock, lane);  // no free slot: the old way
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) atomicExch(&a.mail[jb.item], slot >= 0 ? slot + 1 : -1);
+    return;
+  }
+  // the last plane: collect the others (their warps have passed the counter, the parking takes them a microsecond)
+  const uint8_t* pl[4];
+  int32_t m[4];
+  bool all = true;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    pl[k] = win;
+    m[k] = 0;
+    if (k < ns && k != s) {
+      int32_t v = 0;
+      if (lane == 0) {
+        while ((v = mail_read(&a.mail[first + k])) == 0) B2G_SPIN_PAUSE();
+      }
+      v = __shfl_sync(kFull, v, 0);
+      m[k] = v;
+      if (v > 0) pl[k] = a.stage + (size_t)(v - 1) * (size_t)a.slot_bytes;
+      else all = false;
+    }
+  }
+  __threadfence();
+  if (all) {
+    uint4* o4 = (uint4*)jb.raw;
+    if (ns == 2) {  // 8 elements per lane and step: 8 bytes of each plane -> 16 bytes; 8 steps' loads in flight
+      const int steps = neblock >> 3;
+      int g = lane;
+      for (; g + 7 * 32 < steps; g += 8 * 32) {
+        uint2 p0[8], p1[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          p0[u] = *(const uint2*)(pl[0] + 8 * (g + 32 * u));
+          p1[u] = *(const uint2*)(pl[1] + 8 * (g + 32 * u));
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+          o4[g + 32 * u] = make_uint4(__byte_perm(p0[u].x, p1[u].x, 0x5140), __byte_perm(p0[u].x, p1[u].x, 0x7362),
+                                      __byte_perm(p0[u].y, p1[u].y, 0x5140), __byte_perm(p0[u].y, p1[u].y, 0x7362));
+      }
+      for (; g < steps; g += 32) {
+        const uint2 p0 = *(const uint2*)(pl[0] + 8 * g), p1 = *(const uint2*)(pl[1] + 8 * g);
+        o4[g] = make_uint4(__byte_perm(p0.x, p1.x, 0x5140), __byte_perm(p0.x, p1.x, 0x7362),
+                           __byte_perm(p0.y, p1.y, 0x5140), __byte_perm(p0.y, p1.y, 0x7362));
+      }
+    } else {        // ns == 4: 4 elements per lane and step: 4 bytes of each plane -> 16 bytes
+      const int steps = neblock >> 2;
+      int g = lane;
+      for (; g + 3 * 32 < steps; g += 4 * 32) {
+        uint32_t p[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+#pragma unroll
+          for (int k = 0; k < 4; k++) p[u][k] = *(const uint32_t*)(pl[k] + 4 * (g + 32 * u));
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const uint32_t t0 = __byte_perm(p[u][0], p[u][1], 0x5140), t1 = __byte_perm(p[u][0], p[u][1], 0x7362);
+          const uint32_t u0 = __byte_perm(p[u][2], p[u][3], 0x5140), u1 = __byte_perm(p[u][2], p[u][3], 0x7362);
+          o4[g + 32 * u] = make_uint4(__byte_perm(t0, u0, 0x5410), __byte_perm(t0, u0, 0x7632),
+                                      __byte_perm(t1, u1, 0x5410), __byte_perm(t1, u1, 0x7632));
+        }
+      }
+      for (; g < steps; g += 32) {
+        const uint32_t p0 = *(const uint32_t*)(pl[0] + 4 * g), p1 = *(const uint32_t*)(pl[1] + 4 * g);
+        const uint32_t p2 = *(const uint32_t*)(pl[2] + 4 * g), p3 = *(const uint32_t*)(pl[3] + 4 * g);
+        const uint32_t t0 = __byte_perm(p0, p1, 0x5140), t1 = __byte_perm(p0, p1, 0x7362);
+        const uint32_t u0 = __byte_perm(p2, p3, 0x5140), u1 = __byte_perm(p2, p3, 0x7362);
+        o4[g] = make_uint4(__byte_perm(t0, u0, 0x5410), __byte_perm(t0, u0, 0x7632), __byte_perm(t1, u1, 0x5410),
+                           __byte_perm(t1, u1, 0x7632));
+      }
+    }
+    if (lane == 0) atomicAdd(&a.ctl->paired, 1);
+  } else {
+    scatter_plane(jb.raw, ns, s, win, neblock, lane);
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (k < ns && k != s && m[k] > 0) scatter_plane(jb.raw, ns, k, pl[k], neblock, lane);
+  }
+  __syncwarp();
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (k < ns && k != s && m[k] > 0) atomicExch(&a.slotflag[m[k] - 1], 0);
+  }
+}
+
+// The decoded stream(s) of a work item, from the window into the raw block: a byte plane is paired or scattered, a
+// whole block is un(bit)shuffled (pipeline_backward).
+__device__ __forceinline__ void unfilter_streams(const DecodeArgs& a, const StreamJob& jb, const uint8_t* win) {
   const int lane = lane_id();
   if (jb.scatter) {
-    uint8_t* o = jb.raw + jb.s;
-    const int ns = jb.ns;
-    int i = lane;
-    for (; i + 7 * 32 < jb.neblock; i += 8 * 32) {  // 8 loads in flight, then 8 stores
-      uint8_t v[8];
-#pragma unroll
-      for (int u = 0; u < 8; u++) v[u] = win[i + 32 * u];
-#pragma unroll
-      for (int u = 0; u < 8; u++) o[(size_t)(i + 32 * u) * ns] = v[u];
-    }
-    for (; i < jb.neblock; i += 32) o[(size_t)i * ns] = win[i];
+    const bool pair = a.stage != nullptr && (jb.ns == 2 || jb.ns == 4) && (jb.neblock & 15) == 0 &&
+                      jb.neblock <= a.slot_bytes && (((uintptr_t)jb.raw) & 15) == 0 &&
+                      jb.item - jb.s + jb.ns <= a.pair_cap;  // the same answer for every plane of the block
+    if (pair) pair_planes(a, jb, win);
+    else scatter_plane(jb.raw, jb.ns, jb.s, win, jb.neblock, lane);
   } else if (win != jb.raw) {
     filter_backward(jb.filter, jb.typesize, jb.bsize, win, jb.raw, jb.version, lane, 32);
   }
 }
 
 template <bool Z, bool STAGE, bool SMEM>
-__device__ __forceinline__ int decode_streams(const StreamJob& jb, uint8_t* win, int32_t wbytes, ZWork* zw) {
+__device__ __forceinline__ int decode_streams(const DecodeArgs& a, const StreamJob& jb, uint8_t* win, int32_t wbytes,
+                                              ZWork* zw) {
   // stream directory: each csize tells where the next stream starts (warp-uniform loads)
   int32_t pos = jb.first;
   if (pos <= 0 || pos >= jb.srcsize) return kErrData;
@@ -433,7 +576,7 @@ __device__ __forceinline__ int decode_streams(const StreamJob& jb, uint8_t* win,
     pos += cs > 0 ? cs : (cs < 0 ? 1 : 0);
   }
   __syncwarp();
-  unfilter_streams(jb, win);
+  unfilter_streams(a, jb, win);
   return 0;
 }
 
@@ -488,7 +631,7 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
     StreamJob jb;
     jb.src = ch.src; jb.raw = raw; jb.srcsize = srcsize; jb.first = ld_le32(ch.src + d.hdr + 4 * j);
     jb.s = g.s; jb.s_end = g.s_end; jb.ns = g.ns; jb.neblock = neblock; jb.bsize = bsize; jb.scatter = g.scatter;
-    jb.fmt = d.fmt; jb.filter = d.filter; jb.typesize = d.typesize; jb.version = d.version;
+    jb.fmt = d.fmt; jb.filter = d.filter; jb.typesize = d.typesize; jb.version = d.version; jb.item = item;
     int err;
     bool done = false;
     if (!Z && a.itab != nullptr && item < a.itab_cap && d.rec_base >= 0) {
@@ -506,7 +649,7 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
                                            neblock, (uint4*)(win_s + a.wcap));
           __syncwarp();
           if (got == neblock) {
-            unfilter_streams(jb, win_s);
+            unfilter_streams(a, jb, win_s);
 #ifdef B2G_SIM
             if (lane == 0) sim_two_phase_hits()++;
 #endif
@@ -518,9 +661,9 @@ __global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
       }
     }
     if (done) {}
-    else if (need <= a.wcap) err = decode_streams<Z, true, true>(jb, win_s, a.wcap, zw);
-    else if (direct) err = decode_streams<Z, false, false>(jb, raw, bsize, zw);
-    else err = decode_streams<Z, true, false>(jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw);
+    else if (need <= a.wcap) err = decode_streams<Z, true, true>(a, jb, win_s, a.wcap, zw);
+    else if (direct) err = decode_streams<Z, false, false>(a, jb, raw, bsize, zw);
+    else err = decode_streams<Z, true, false>(a, jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw);
     if (err && lane == 0) set_status(a.res, c, err);
     __syncwarp();  // the window is free for the next item
   }

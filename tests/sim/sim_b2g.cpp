@@ -10,13 +10,15 @@ using namespace b2g;
 
 static size_t au(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+static int g_last_paired = 0;
+
 extern "C" {
 
 // Decompress a batch.  grid = number of simulated persistent CTAs; win_bytes = shared window of one warp (streams
 // that need more use the slab path).  out[i] = nbytes or 0, status[i] = 0 or error.
 int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes, void* const* dsts,
                          const int32_t* caps, int32_t* out, int32_t* status, int win_bytes, int max_block, int grid,
-                         int zstd_ok, int two_phase) {
+                         int zstd_ok, int two_phase, int pair) {
   std::vector<DChunk> ch(n);
   std::vector<DInfo> info(n);
   std::vector<DResult> res(n);
@@ -51,18 +53,30 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   da.chunks = ch.data(); da.info = info.data(); da.res = res.data(); da.base = base.data(); da.ctl = &ctl[0];
   da.n = n; da.wcap = win_bytes; da.wstride = win_bytes + kSeqGroupSmem; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
   da.itab = itab_cap > 0 ? itab.data() : nullptr; da.itab_cap = (int32_t)itab_cap; da.rec = recs.data();
+  // plane pairing: few slots on purpose (the no-free-slot path must run too); pair == 0 switches it off
+  long long pair_cap = 0;
+  for (int i = 0; i < n; i++) pair_cap += ((long long)std::max(caps[i], 0) / 64 + 2) * kMaxStreams;
+  const int nslots = pair == 2 ? 1 : 3;
+  std::vector<uint8_t> stage((size_t)nslots * win_bytes + 16);
+  std::vector<int32_t> pairmeta(nslots + 4 * pair_cap + 4, 0);
+  da.stage = pair ? stage.data() : nullptr;
+  da.slotflag = pairmeta.data(); da.mail = da.slotflag + nslots; da.blkcnt = da.mail + 2 * pair_cap;
+  da.nslots = nslots; da.slot_bytes = win_bytes; da.pair_cap = (int32_t)pair_cap;
   if (itab_cap > 0) cusim::launch(dim3(grid), dim3(kParseThreads), kParseSmemBytes, [&] { k_parse(da); });
   cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<false>(da); });
   if (zstd_ok) {
     da.base = base.data() + (n + 1);
     da.ctl = &ctl[1];
     da.wstride = win_bytes + (int)au(sizeof(ZWork), 16);
+    da.mail += pair_cap; da.blkcnt += pair_cap;
     cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<true>(da); });
   }
   for (int i = 0; i < n; i++) {
     status[i] = res[i].status;
     out[i] = res[i].status < 0 ? 0 : res[i].out_bytes;
   }
+  g_last_paired = ctl[0].paired + ctl[1].paired;
+  for (int k = 0; k < nslots; k++) if (pairmeta[k] != 0) return -1;  // a staging slot was never given back
   return 0;
 }
 
@@ -162,5 +176,6 @@ int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int
 
 unsigned long long sim_collectives() { return cusim::S().collectives; }
 unsigned long long sim_two_phase_hits() { return b2g::sim_two_phase_hits(); }
+int sim_last_paired() { return g_last_paired; }
 
 }  // extern "C"

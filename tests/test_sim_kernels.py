@@ -316,6 +316,40 @@ def test_two_phase_long_literal_runs_in_place(codec, gap, mlen):
                 assert st == 0 and np.array_equal(out, s) and np.array_equal(e, s), (ts, bs, wb)
 
 
+# ---- plane pairing (parked planes, the last one writes the block interleaved) -----------------------------------------
+@pytest.mark.parametrize("ts", [2, 4])
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ, _data.ZSTD])
+def test_plane_pairing_matches_plain_scatter(ts, codec):
+    """Split shuffled blocks decode identically with pairing on (3 staging slots), starved (1 slot: planes fall back to
+    scattering their own bytes, blocks end up mixed) and off; full blocks are actually paired."""
+    if codec == _data.ZSTD and not HAVE_REF:
+        pytest.skip("zstd chunks need the reference encoder")
+    srcs = [_data.make_data(k, 4 * 32768 + extra, ts, seed=3) for k, extra in
+            (("ramp", 0), ("f32", 4 * 17), ("sparse", 0), ("random", 32768), ("zeros", 0))]
+    if codec == _data.ZSTD:
+        chunks = [_libs.ref_compress(codec, 3, ts, _data.SHUFFLE, 32768, s) for s in srcs]
+    else:
+        chunks = [c for _, c in _sim.compress_batch(srcs, codec, 9, ts, _data.SHUFFLE, 32768)]
+    got = {}
+    for pair in (1, 2, 0):
+        for tp in (0, 1):
+            res = _sim.decompress_batch(chunks, grid=3, two_phase=tp, pair=pair)
+            paired = _sim.lib().sim_last_paired()
+            for s, (st, out) in zip(srcs, res):
+                assert st == 0 and np.array_equal(out, s.view(np.uint8).reshape(-1)), (pair, tp)
+            got[(pair, tp)] = paired
+    assert got[(1, 0)] >= 8 and got[(1, 1)] >= 8
+    assert got[(0, 0)] == 0 and got[(0, 1)] == 0
+
+
+def test_plane_pairing_unaligned_destination_falls_back():
+    src = _data.make_data("ramp", 3 * 32768, 2, seed=5)
+    (st, chunk), = _sim.compress_batch([src], _data.LZ4, 9, 2, _data.SHUFFLE, 32768)
+    assert st == 0
+    (st, out), = _sim.decompress_batch([chunk])
+    assert st == 0 and np.array_equal(out, src)
+
+
 # ---- whole chunks: compress -----------------------------------------------------------------------------------------
 def _compress_cases():
     seen = set()
