@@ -329,11 +329,22 @@ def run_b2g(args, rank, world, local_rank):
     kern = {"k_decode": dec_ms, "k_compress": comp_ms}
     dom = max(kern, key=kern.get)
 
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the same workload, from the committed ncu --set full
+    # capture (profiles/traffic.json names the report it was read from); never measured inside this run
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            traffic = json.load(fh)
+    except Exception:
+        traffic = {}
+
     def roof(name):
         t = kern[name]
         a = alg_bytes / (t * 1e-3) / 1e9 if t > 0 else 0.0
+        tr = traffic.get(name)
         return {"kernel": name, "bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
-                "traffic": None, "ms_per_launch": t, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src}
+                "traffic": (tr["dram_bytes_read"] + tr["dram_bytes_write"]) if tr else None,
+                "traffic_source": traffic.get("source") if tr else None,
+                "ms_per_launch": t, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src}
 
     roofline = roof(dom)
     roofline["kernels"] = {k: roof(k) for k in kern}

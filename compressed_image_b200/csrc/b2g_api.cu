@@ -159,7 +159,7 @@ int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   const size_t per = (size_t)g.win + (size_t)g.htab + kEncWorkBytes;
   int best = 0;
   g.warps = 1;
-  for (int w : {1, 2, 3, 4, 6, 8}) {
+  for (int w = 1; w <= 8; w++) {  // k_compress is bounded to 256 threads
     const size_t cta = (size_t)w * per;
     if (cta > 227 * 1024) break;
     int n = (int)((228 * 1024) / (cta + 1024));
@@ -206,7 +206,7 @@ int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
   g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : kSeqGroupSmem);  // + the record executor's scratch
   int best = 0;
   g.warps = 1;
-  for (int w : {1, 2, 3, 4, 6, 8}) {
+  for (int w = 1; w <= 16; w++) {
     const size_t cta = (size_t)w * g.wstride;
     if (cta > 227 * 1024) break;
     int n = (int)((228 * 1024) / (cta + 1024));

@@ -581,7 +581,7 @@ __device__ __forceinline__ int decode_streams(const DecodeArgs& a, const StreamJ
 }
 
 template <bool Z>
-__global__ void __launch_bounds__(256, 2) k_decode(DecodeArgs a) {
+__global__ void __launch_bounds__(512, 1) k_decode(DecodeArgs a) {
   const int warp = warp_id(), lane = lane_id();
   uint8_t* win_s = dyn_smem() + (size_t)warp * (size_t)a.wstride;
   ZWork* zw = Z ? (ZWork*)(win_s + a.wcap) : nullptr;
