@@ -153,9 +153,10 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       }
       __syncwarp();  // every table read of the step happens before any table write
 #pragma unroll
-      for (int j = 0; j < 4; j++)
+      for (int j = 0; j < 4; j++) {
         if (live[j] && (peers[j] >> lane) == 1u) w.htab[h[j]] = (uint16_t)(bbase + 32 * j + lane);  // last of its hash group
-      __syncwarp();  // ... and every write before the next step's reads
+        __syncwarp();  // group j + 1 overwrites group j where their hashes meet (most recent wins), and every write
+      }                // is done before the next step's reads
       gb = gbn;
     }
     __syncwarp();
@@ -179,7 +180,19 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       int p = tbase + g * 32 + b;
       const int dist = (int)w.off[g * 32 + b];
       int c = p - dist;
-      int ml = 4 + warp_match_len(in + p + 4, in + c + 4, mlimit - (p + 4), lane);
+      // Match length beyond the verified 4 bytes.  Most matches of a noisy plane end within the next 4 bytes: one
+      // warp-uniform word compare settles those, the warp-wide compare only runs for the longer ones (same result).
+      int ml;
+      {
+        const int room = mlimit - (p + 4);
+        const uint32_t x = ld32_any(in + p + 4) ^ ld32_any(in + c + 4);  // p + 7 <= n - 5: inside the stream
+        if (x != 0u || room <= 4) {
+          const int e = x ? ((__ffs((int)x) - 1) >> 3) : 4;
+          ml = 4 + max(0, min(e, room));
+        } else {
+          ml = 8 + warp_match_len(in + p + 8, in + c + 8, room - 4, lane);
+        }
+      }
       if (!LZ4 && dist - 1 >= kBlzMaxDistance && ml < 8) {  // a 4-byte far token does not pay for a short match
         ip = p + 1;
         continue;
