@@ -274,8 +274,16 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         const int j = __ffs((int)lm) - 1;
         lm &= lm - 1;
         const int s = __shfl_sync(kFull, start, j), d = __shfl_sync(kFull, litpos, j), l = __shfl_sync(kFull, lit, j);
-        if (LZ4) copy_bytes(out + d, in + s, l, lane, 32);
-        else blosclz_put_literals(in, s, l, out, d, lane);
+        if (LZ4) {
+          if (l <= 64) {  // the usual case: one or two bytes per lane, no alignment bookkeeping
+            if (lane < l) out[d + lane] = in[s + lane];
+            if (lane + 32 < l) out[d + 32 + lane] = in[s + 32 + lane];
+          } else {
+            copy_bytes(out + d, in + s, l, lane, 32);
+          }
+        } else {
+          blosclz_put_literals(in, s, l, out, d, lane);
+        }
       }
       op += total;
     }
