@@ -738,12 +738,12 @@ __device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const u
     if (ts == 2) {
       const uint32_t sel = s ? 0x7531u : 0x6420u;
       int g = lane;
-      for (; g + 3 * nthr < groups; g += 4 * nthr) {  // four loads in flight
-        uint4 v[4];
+      for (; g + 7 * nthr < groups; g += 8 * nthr) {  // eight loads in flight
+        uint4 v[8];
 #pragma unroll
-        for (int u = 0; u < 4; u++) v[u] = r4[g + u * nthr];
+        for (int u = 0; u < 8; u++) v[u] = r4[g + u * nthr];
 #pragma unroll
-        for (int u = 0; u < 4; u++)
+        for (int u = 0; u < 8; u++)
           *(uint2*)(win + 8 * (g + u * nthr)) = make_uint2(__byte_perm(v[u].x, v[u].y, sel), __byte_perm(v[u].z, v[u].w, sel));
       }
       for (; g < groups; g += nthr) {

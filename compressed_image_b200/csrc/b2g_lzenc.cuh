@@ -180,6 +180,10 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       int p = tbase + g * 32 + b;
       const int dist = (int)w.off[g * 32 + b];
       int c = p - dist;
+      // the bytes in front of the match and of its source, for the backward extension below: fetched here so that their
+      // latency overlaps the forward compare
+      const bool can_back = p > lastend && c > 0;
+      const uint32_t pb = in[can_back ? p - 1 : 0], cb = in[can_back ? c - 1 : 0];
       // Match length beyond the verified 4 bytes.  Most matches of a noisy plane end within the next 4 bytes: one
       // warp-uniform word compare settles those, the warp-wide compare only runs for the longer ones (same result).
       int ml;
@@ -197,7 +201,10 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         ip = p + 1;
         continue;
       }
-      while (p > lastend && c > 0 && in[p - 1] == in[c - 1]) { p--; c--; ml++; }  // extend over pending literals
+      if (can_back && pb == cb) {  // extend over pending literals
+        p--; c--; ml++;
+        while (p > lastend && c > 0 && in[p - 1] == in[c - 1]) { p--; c--; ml++; }
+      }
       if (lane == 0) { w.sp[nseq] = (uint32_t)p; w.sml[nseq] = (uint32_t)ml; w.so[nseq] = (uint16_t)dist; }
       nseq++;
       lastend = ip = p + ml;
