@@ -62,6 +62,8 @@ __device__ __forceinline__ void lz_literal_copy(uint8_t* out, int op, const uint
 // in a stream that compresses; when a sequence would, -2 is returned and the caller decodes from the original bytes.
 // Header bytes are fetched with warp-uniform loads (one broadcast each), and the next token is fetched before the
 // copies of the current sequence are issued, so its latency overlaps them.
+constexpr int kLz4Zone = 600;
+
 template <bool INPLACE>
 __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8_t* out, int cap, int a) {
   const int lane = lane_id();
@@ -70,6 +72,47 @@ __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8
   uint32_t tok = in[0];
   uint32_t nxt = n > 1 ? in[1] : 0u;
   for (;;) {
+    // ---- the zone: far from both ends of the stream ------------------------------------------------------------------
+    // A sequence whose length fields take at most one extension byte each produces <= 269 + 273 bytes from <= 276, so
+    // kLz4Zone bytes away from the end of the input and of the output none of the end-of-stream rules (lz4.c:2279-2320,
+    // 2419-2423) and none of the input bounds can fire: they are not evaluated.  Anything else (a 255 extension byte,
+    // the zone's edge) drops to the general sequence below, which starts again from the same token.
+    while (op <= cap - kLz4Zone && ip <= n - kLz4Zone) {
+      int lit = (int)(tok >> 4);
+      int pos = ip + 1;
+      if (lit == 15) {
+        if (nxt == 255u) break;
+        lit += (int)nxt;
+        pos++;
+      }
+      const int opos = pos + lit;
+      const uint32_t offset = (uint32_t)in[opos] | ((uint32_t)in[opos + 1] << 8);
+      int ipn = opos + 2;
+      uint32_t t0 = in[ipn], t1 = in[ipn + 1];
+      int ml = (int)(tok & 15u);
+      if (ml == 15 && t0 == 255u) break;  // nothing has been written yet
+      const int cpy = op + lit;
+      lz_literal_copy<INPLACE>(out, op, in, pos, lit, a + pos - op, lane);
+      if (ml == 15) {
+        ml += (int)t0;
+        ipn++;
+        t0 = t1;
+        t1 = in[ipn + 1];
+      }
+      ml += 4;
+      if ((int)offset > cpy) return -1;
+      const int mend = cpy + ml;
+      if (INPLACE && mend > a + ipn) return -2;
+      __syncwarp();
+      if (offset == 0) fill_bytes(out + cpy, 0, ml, lane, 32);
+      else if (ml <= 32 && (int)offset >= ml) { if (lane < ml) out[cpy + lane] = out[cpy - (int)offset + lane]; }
+      else lz_match_copy(out, cpy, (int)offset, ml, lane);
+      op = mend;
+      ip = ipn;
+      tok = t0;
+      nxt = t1;
+    }
+    // ---- one general sequence ---------------------------------------------------------------------------------------
     if (ip >= n) return -1;
     int lit = (int)(tok >> 4);
     int pos = ip + 1;
