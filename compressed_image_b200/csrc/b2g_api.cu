@@ -191,7 +191,7 @@ int set_geometry(b2g_ctx* c, int blocksize) {
 }
 
 size_t slab_stride(const b2g_ctx* c) {
-  return align_up((size_t)decode_window_bytes(std::max(c->blocksize, c->p.blocksize)) + 256, 256);
+  return align_up((size_t)decode_window_bytes(std::max(c->blocksize, c->p.blocksize), kFmtBlosclz) + 256, 256);
 }
 
 // Decode launch geometry for streams of `stream_bytes`: every warp is an independent worker with its own window, so
@@ -200,10 +200,10 @@ struct DecGeom {
   int wcap, wstride, warps, grid;
   size_t smem;
 };
-int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
+int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g, bool any_blosclz = true) {
   if (stream_bytes > 96 * 1024) stream_bytes = 16 * 1024;  // such streams decode through the global slab anyway
-  g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1)), 1024);
-  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : kSeqGroupSmem);  // + the record executor's scratch
+  g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1), any_blosclz ? kFmtBlosclz : kFmtLz4), 1024);
+  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : (c->two_phase ? kSeqGroupSmem : 0));  // + replay scratch
   int best = 0;
   g.warps = 1;
   for (int w = 1; w <= 16; w++) {
@@ -226,10 +226,12 @@ int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g) {
   return 0;
 }
 
+// any_blosclz = false: the caller knows that no chunk of the batch is blosclz (the windows are then sized for lz4; a
+// blosclz stream that shows up anyway decodes through the global slab)
 int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_t s, bool want_zstd, int stream_bytes,
-                   DResult* h_res = nullptr) {
+                   DResult* h_res = nullptr, bool any_blosclz = true) {
   DecGeom g, gz;
-  if (int rc = decode_geometry(c, stream_bytes, false, g)) return rc;
+  if (int rc = decode_geometry(c, stream_bytes, false, g, any_blosclz)) return rc;
   gz = g;
   if (want_zstd) if (int rc = decode_geometry(c, stream_bytes, true, gz)) return rc;
   // slab: windows for streams larger than the shared-memory window, one per warp of the grid
@@ -520,7 +522,8 @@ int b2g_decompress_batch_device(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda
     h[i].src_bytes = chunks[i].src_bytes;
     h[i].dst_cap = chunks[i].dst_capacity;
   }
-  int rc = enqueue_decode(c, L, h, n, s, c->p.codec == B2G_ZSTD, c->stream_hint);
+  int rc = enqueue_decode(c, L, h, n, s, c->p.codec == B2G_ZSTD, c->stream_hint, nullptr,
+                          c->p.codec != B2G_LZ4 && c->p.codec != B2G_LZ4HC);  // an lz4 context sizes its windows for lz4
   if (rc) c->pend = nullptr;
   return rc;
 }
@@ -624,7 +627,7 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
   std::vector<size_t> in_off(n), out_off(n), in_len(n), out_len(n), payload(n);
   size_t in_total = 0, out_total = 0;
   int maxblock = 0, maxstream = 0;
-  bool any_zstd = false;
+  bool any_zstd = false, any_blosclz = false;
   for (int i = 0; i < n; i++) {
     const uint8_t* src = (const uint8_t*)chunks[i].src;
     int32_t avail = chunks[i].src_bytes;
@@ -642,6 +645,7 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
         maxstream = std::max(maxstream, split ? bs / ts : bs);
       }
       if ((src[2] >> 5) == kFmtZstd) any_zstd = true;
+      if ((src[2] >> 5) == kFmtBlosclz && !(src[2] & kFlagMemcpyed)) any_blosclz = true;
     } else if (src && avail > 0) {
       take = (size_t)avail;
     }
@@ -693,7 +697,7 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
       d.dst_cap = chunks[i].dst_capacity;
       if (in_len[i]) CU(cudaMemcpyAsync((void*)d.src, chunks[i].src, in_len[i], cudaMemcpyHostToDevice, s));
     }
-    if (int rc = enqueue_decode(c, L, desc + lo, cnt, s, any_zstd, std::max(maxstream, 1), res + lo)) return rc;
+    if (int rc = enqueue_decode(c, L, desc + lo, cnt, s, any_zstd, std::max(maxstream, 1), res + lo, any_blosclz)) return rc;
     for (int q = lo; q < lo + cnt;) {  // one copy per run of neighbouring outputs
       const int i = ord[q];
       size_t len = out_len[i];

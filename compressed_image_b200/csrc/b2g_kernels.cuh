@@ -246,8 +246,11 @@ struct DecodeArgs {
 };
 
 // Window bytes needed to decode a stream of `neblock` bytes with its compressed bytes staged in place above the output.
-__host__ __device__ __forceinline__ int decode_window_bytes(int neblock) {
-  return (neblock + (neblock >> 5) + 64 + 15) & ~15;  // blosclz literal runs expand by 1/32
+// A stream that is stored compressed is shorter than neblock, so the window only has to leave the output a head start:
+// blosclz literal runs expand by 1/32; an LZ4 (or zstd: no staging) stream needs a small margin only.
+__host__ __device__ __forceinline__ int decode_window_bytes(int neblock, int fmt) {
+  if (fmt == kFmtBlosclz) return (neblock + (neblock >> 5) + 64 + 15) & ~15;
+  return (neblock + 80 + 15) & ~15;
 }
 
 // item number inside a chunk -> (block j, streams [s, s_end) of ns, block bytes, stream bytes)
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(kParseThreads) k_parse(DecodeArgs a) {
         const DGeom g = decode_geometry_of(d, item - d.item_base);
         const uint8_t* src = a.chunks[c].src;
         const int32_t srcsize = min(a.chunks[c].src_bytes, d.cbytes);
-        const int32_t need = decode_window_bytes(g.neblock);
+        const int32_t need = decode_window_bytes(g.neblock, d.fmt);
         int32_t pos = ld_le32(src + d.hdr + 4 * g.j);
         bool ok = need <= a.wcap && g.neblock > 0 && pos > 0 && pos < srcsize;
         int32_t cs = 0;
@@ -625,7 +628,7 @@ __global__ void __launch_bounds__(512, 1) k_decode(DecodeArgs a) {
     uint8_t* raw = ch.dst + (size_t)j * d.blocksize;
     const int32_t srcsize = min(ch.src_bytes, d.cbytes);
     const bool direct = !g.scatter && d.filter == kFilterNone;  // no filter: the window is only a staging area
-    const int32_t need = decode_window_bytes(g.scatter ? neblock : bsize);
+    const int32_t need = decode_window_bytes(g.scatter ? neblock : bsize, d.fmt);
     // Three window kinds, three instantiations: the shared-memory one must be its own code path so that every access
     // of the byte-serial decoder compiles to LDS / STS instead of generic loads and stores.
     StreamJob jb;

@@ -47,7 +47,7 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   pa.rec_cap = rec_cap;
   cusim::launch(dim3(1), dim3(kPlanThreads), kPlanSmemBytes, [&] { k_plan_decode(pa); });
   const int warps = 2;  // independent workers per simulated CTA
-  const size_t stride = au((size_t)decode_window_bytes(max_block) + 256, 256);
+  const size_t stride = au((size_t)decode_window_bytes(max_block, kFmtBlosclz) + 256, 256);
   std::vector<uint8_t> slab(stride * grid * warps + 256);
   DecodeArgs da;
   da.chunks = ch.data(); da.info = info.data(); da.res = res.data(); da.base = base.data(); da.ctl = &ctl[0];
