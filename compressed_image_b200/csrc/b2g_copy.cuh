@@ -59,6 +59,13 @@ __device__ __forceinline__ void fill_bytes(uint8_t* dst, uint8_t value, int n, i
   for (int i = (groups << 4) + tid; i < rem; i += nthr) d[i] = value;
 }
 
+// lane % d for 0 <= lane < 32, 1 <= d < 32 (warp-uniform d) without an integer division: (lane + 0.5) / d is never
+// within rounding distance of an integer.
+__device__ __forceinline__ int lane_mod(int lane, int d) {
+  const int q = (int)(((float)lane + 0.5f) * (1.0f / (float)d));
+  return lane - q * d;
+}
+
 // LZ77 back-reference copy by one warp: out[op .. op+len) = out[op-dist ..] with byte-serial (overlapping)
 // semantics.  dist >= 1.  The caller has made earlier writes visible (__syncwarp) before calling.
 __device__ __forceinline__ void lz_match_copy(uint8_t* out, int op, int dist, int len, int lane) {

@@ -281,13 +281,6 @@ __device__ __forceinline__ int seq_parse_warp(LaneParse& L, bool active, bool lz
   return (state == kStepDone && L.op == L.cap) ? L.nrec : 0;
 }
 
-// lane % d for 0 <= lane < 32, 1 <= d < 32 (warp-uniform d) without an integer division: (lane + 0.5) / d is never
-// within rounding distance of an integer.
-__device__ __forceinline__ int lane_mod(int lane, int d) {
-  const int q = (int)(((float)lane + 0.5f) * (1.0f / (float)d));
-  return lane - q * d;
-}
-
 // Replays `nseq` records into win[0..cap); the stream's payload is staged at win + a (in place: a >= slack has been
 // checked by the caller, so no write ever reaches input that is still to be read).  `sq` = 32 x uint4 of the warp's
 // shared memory.  Every record is bounds-checked again here (per lane, 32 at a time): the records live in global memory
