@@ -58,6 +58,10 @@ def lib():
         L.b2g_wait.argtypes = [vp]
         L.b2g_chunk_sizes.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.b2g_filter_device.argtypes = [vp, ci, ci, ci, ci, vp, vp, C.c_int64, C.c_int32, vp]
+        L.b2g_interleave_device.argtypes = [vp, ci, ci, C.POINTER(vp), vp, C.c_int64, vp]
+        L.b2g_deinterleave_device.argtypes = [vp, ci, ci, vp, C.POINTER(vp), C.c_int64, vp]
+        L.b2g_interleave_device.restype = ci
+        L.b2g_deinterleave_device.restype = ci
         L.b2g_launch_count.argtypes = [vp]
         L.b2g_launch_count.restype = C.c_int64
         L.b2g_last_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -72,7 +76,8 @@ def lib():
 
 EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
            "b2g_decompress_batch_async", "b2g_compress_batch_device",
-           "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_launch_count",
+           "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
+           "b2g_deinterleave_device", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 
 
@@ -162,6 +167,20 @@ class Context:
                                      blocksize, stream)
         if rc < 0:
             raise B2GError(rc, "b2g_filter_device")
+
+    def interleave_device(self, typesize, plane_ptrs, interleaved_ptr, n_elems, stream=None):
+        """interleaved[i * nch + c] = plane[c][i] on device-resident buffers (image_algo.h:34-65); stream-ordered."""
+        arr = (C.c_void_p * max(len(plane_ptrs), 1))(*plane_ptrs)
+        rc = lib().b2g_interleave_device(self._h, typesize, len(plane_ptrs), arr, interleaved_ptr, n_elems, stream)
+        if rc < 0:
+            raise B2GError(rc, "b2g_interleave_device")
+
+    def deinterleave_device(self, typesize, interleaved_ptr, plane_ptrs, n_elems, stream=None):
+        """plane[c][i] = interleaved[i * nch + c] on device-resident buffers (image_algo.h:84-111); stream-ordered."""
+        arr = (C.c_void_p * max(len(plane_ptrs), 1))(*plane_ptrs)
+        rc = lib().b2g_deinterleave_device(self._h, typesize, len(plane_ptrs), interleaved_ptr, arr, n_elems, stream)
+        if rc < 0:
+            raise B2GError(rc, "b2g_deinterleave_device")
 
     @property
     def launches(self):

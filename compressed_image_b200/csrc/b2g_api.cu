@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../include/b2g.h"
+#include "b2g_interleave.cuh"
 #include "b2g_kernels.cuh"
 #include "b2g_plan.h"
 
@@ -459,6 +460,110 @@ int use_device(b2g_ctx* c) {
 
 }  // namespace
 
+// ---- interleave / deinterleave -------------------------------------------------------------------
+namespace {
+
+template <int TS, int NCH>
+void launch_ilv_vec(bool to_interleaved, void* inter, const IlvPlanes4& pl, int64_t groups, int grid, cudaStream_t s) {
+  if (to_interleaved) k_interleave_vec<TS, NCH><<<grid, kIlvThreads, 0, s>>>((uint4*)inter, pl, groups);
+  else k_deinterleave_vec<TS, NCH><<<grid, kIlvThreads, 0, s>>>((const uint4*)inter, pl, groups);
+}
+
+template <int TS>
+bool launch_ilv_vec_nch(int nch, bool to_interleaved, void* inter, const IlvPlanes4& pl, int64_t groups, int grid, cudaStream_t s) {
+  switch (nch) {
+    case 2: launch_ilv_vec<TS, 2>(to_interleaved, inter, pl, groups, grid, s); return true;
+    case 3: launch_ilv_vec<TS, 3>(to_interleaved, inter, pl, groups, grid, s); return true;
+    case 4: launch_ilv_vec<TS, 4>(to_interleaved, inter, pl, groups, grid, s); return true;
+    default: return false;
+  }
+}
+
+int interleave_device(b2g_ctx* c, bool to_interleaved, int typesize, int nch, void* const* planes, void* inter, int64_t n,
+                      void* cuda_stream) {
+  if (!c || !planes || typesize <= 0 || typesize > 255 || nch <= 0 || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (n == 0) return 0;
+  if (!inter) return B2G_ERR_INVALID_PARAM;
+  for (int k = 0; k < nch; k++)
+    if (!planes[k]) return B2G_ERR_INVALID_PARAM;
+  if (int rc = use_device(c)) return rc;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->lanes[0].stream;
+  const int64_t plane_bytes = n * typesize;
+  if (nch == 1) {                                   // one channel: the two layouts are the same bytes
+    if (to_interleaved) CU(cudaMemcpyAsync(inter, planes[0], (size_t)plane_bytes, cudaMemcpyDeviceToDevice, s));
+    else CU(cudaMemcpyAsync(planes[0], inter, (size_t)plane_bytes, cudaMemcpyDeviceToDevice, s));
+    return 0;
+  }
+  int64_t done = 0;                                 // elements handled by the vector kernel
+  bool vec_ok = nch <= 4 && (typesize == 1 || typesize == 2 || typesize == 4 || typesize == 8) && ((uintptr_t)inter & 15) == 0;
+  for (int k = 0; k < nch && vec_ok; k++) vec_ok = ((uintptr_t)planes[k] & 15) == 0;
+  if (vec_ok && plane_bytes >= 16) {
+    const int64_t groups = plane_bytes / 16;
+    IlvPlanes4 pl{};
+    for (int k = 0; k < nch; k++) pl.p[k] = planes[k];
+    const int grid = (int)std::min<int64_t>((groups + kIlvThreads - 1) / kIlvThreads, (int64_t)c->sms * 16);
+    bool ok = false;
+    switch (typesize) {
+      case 1: ok = launch_ilv_vec_nch<1>(nch, to_interleaved, inter, pl, groups, grid, s); break;
+      case 2: ok = launch_ilv_vec_nch<2>(nch, to_interleaved, inter, pl, groups, grid, s); break;
+      case 4: ok = launch_ilv_vec_nch<4>(nch, to_interleaved, inter, pl, groups, grid, s); break;
+      case 8: ok = launch_ilv_vec_nch<8>(nch, to_interleaved, inter, pl, groups, grid, s); break;
+    }
+    if (ok) {
+      c->launches++;
+      CU(cudaGetLastError());
+      done = groups * (16 / typesize);
+    }
+  }
+  // any other channel count whose pixel is whole words: tiles through shared memory
+  bool tile_ok = done == 0 && nch <= kIlvMaxPlanes && (typesize == 1 || typesize == 2 || typesize == 4 || typesize == 8) &&
+                 (nch * typesize) % 4 == 0 && ((uintptr_t)inter & 3) == 0 && (nch * typesize / 4 | 1) * 32 <= kIlvTileWords;
+  for (int k = 0; k < nch && tile_ok; k++) tile_ok = ((uintptr_t)planes[k] & 3) == 0;
+  if (tile_ok && plane_bytes >= 4) {
+    const int W = nch * typesize / 4, psw = W | 1;
+    const int P = std::min(1024, kIlvTileWords / psw / 32 * 32);
+    const int64_t nv = typesize >= 4 ? n : n / (4 / typesize) * (4 / typesize);
+    IlvPlanes pl{};
+    for (int k = 0; k < nch; k++) pl.p[k] = planes[k];
+    const int grid = (int)std::min<int64_t>((nv + P - 1) / P, (int64_t)c->sms * 6);
+#define B2G_ILV_TILE(TS)                                                                                                 \
+  if (to_interleaved) k_interleave_tile<TS><<<grid, kIlvThreads, 0, s>>>((uint32_t*)inter, pl, nch, W, psw, P, nv);      \
+  else k_deinterleave_tile<TS><<<grid, kIlvThreads, 0, s>>>((const uint32_t*)inter, pl, nch, W, psw, P, nv)
+    switch (typesize) {
+      case 1: B2G_ILV_TILE(1); break;
+      case 2: B2G_ILV_TILE(2); break;
+      case 4: B2G_ILV_TILE(4); break;
+      default: B2G_ILV_TILE(8); break;
+    }
+#undef B2G_ILV_TILE
+    c->launches++;
+    CU(cudaGetLastError());
+    done = nv;
+  }
+  if (done < n) {                                   // the rest (or everything), kIlvMaxPlanes channels per launch
+    const int64_t rest = n - done;
+    for (int c0 = 0; c0 < nch; c0 += kIlvMaxPlanes) {
+      const int count = std::min(kIlvMaxPlanes, nch - c0);
+      IlvPlanes pl{};
+      for (int k = 0; k < count; k++) pl.p[k] = planes[c0 + k];
+      if (to_interleaved) {
+        const int64_t total = rest * count;
+        const int grid = (int)std::min<int64_t>((total + kIlvThreads - 1) / kIlvThreads, (int64_t)c->sms * 16);
+        k_interleave_elems<<<grid, kIlvThreads, 0, s>>>((uint8_t*)inter, pl, typesize, nch, c0, count, done, n);
+      } else {
+        const int gx = (int)std::min<int64_t>((rest + kIlvThreads - 1) / kIlvThreads, (int64_t)c->sms * 16);
+        k_deinterleave_elems<<<dim3((unsigned)gx, (unsigned)count), kIlvThreads, 0, s>>>((const uint8_t*)inter, pl, typesize, nch,
+                                                                                        c0, count, done, n);
+      }
+      c->launches++;
+      CU(cudaGetLastError());
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
 extern "C" {
 
 b2g_ctx* b2g_create(const b2g_params* params) {
@@ -855,6 +960,16 @@ int b2g_filter_device(b2g_ctx* c, int filter, int forward, int typesize, int for
   c->launches++;
   CU(cudaGetLastError());
   return 0;
+}
+
+int b2g_interleave_device(b2g_ctx* c, int typesize, int nchannels, const void* const* planes, void* interleaved,
+                          int64_t n_elems, void* cuda_stream) {
+  return interleave_device(c, true, typesize, nchannels, (void* const*)planes, interleaved, n_elems, cuda_stream);
+}
+
+int b2g_deinterleave_device(b2g_ctx* c, int typesize, int nchannels, const void* interleaved, void* const* planes,
+                            int64_t n_elems, void* cuda_stream) {
+  return interleave_device(c, false, typesize, nchannels, planes, (void*)interleaved, n_elems, cuda_stream);
 }
 
 int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }

@@ -133,6 +133,17 @@ B2G_API int b2g_chunk_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes,
 B2G_API int b2g_filter_device(b2g_ctx* ctx, int filter, int forward, int typesize, int format_version,
                               const void* src, void* dst, int64_t n, int32_t blocksize, void* cuda_stream);
 
+/* Replace compressed::image_algo::interleave<T> / deinterleave<T> (compressed_image/include/compressed/
+ * image_algo.h:34-65, :84-111; call site image.h:1880) for device-resident buffers:
+ *     interleaved[i * nchannels + c] = planes[c][i],   elements of `typesize` bytes, i < n_elems.
+ * `planes` is a HOST array of nchannels DEVICE pointers (n_elems * typesize bytes each); `interleaved` holds
+ * n_elems * nchannels * typesize bytes.  Enqueued on the stream, not waited for.  nchannels <= 0 is
+ * B2G_ERR_INVALID_PARAM (the reference throws std::invalid_argument for an empty span list). */
+B2G_API int b2g_interleave_device(b2g_ctx* ctx, int typesize, int nchannels, const void* const* planes,
+                                  void* interleaved, int64_t n_elems, void* cuda_stream);
+B2G_API int b2g_deinterleave_device(b2g_ctx* ctx, int typesize, int nchannels, const void* interleaved,
+                                    void* const* planes, int64_t n_elems, void* cuda_stream);
+
 /* Number of kernels this library has launched through `ctx` since creation (bench.py's gpu_launches). */
 B2G_API int64_t b2g_launch_count(const b2g_ctx* ctx);
 /* Milliseconds the last batch's kernels took on the device (CUDA events on the launching stream), split by
