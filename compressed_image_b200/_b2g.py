@@ -61,6 +61,10 @@ def lib():
         L.b2g_interleave_device.argtypes = [vp, ci, ci, C.POINTER(vp), vp, C.c_int64, vp]
         L.b2g_deinterleave_device.argtypes = [vp, ci, ci, vp, C.POINTER(vp), C.c_int64, vp]
         L.b2g_interleave_device.restype = ci
+        L.b2g_interleave.argtypes = [vp, ci, ci, C.POINTER(vp), vp, C.c_int64]
+        L.b2g_deinterleave.argtypes = [vp, ci, ci, vp, C.POINTER(vp), C.c_int64]
+        L.b2g_interleave.restype = ci
+        L.b2g_deinterleave.restype = ci
         L.b2g_deinterleave_device.restype = ci
         L.b2g_launch_count.argtypes = [vp]
         L.b2g_launch_count.restype = C.c_int64
@@ -77,7 +81,7 @@ def lib():
 EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
            "b2g_decompress_batch_async", "b2g_compress_batch_device",
            "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
-           "b2g_deinterleave_device", "b2g_launch_count",
+           "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 
 
@@ -181,6 +185,19 @@ class Context:
         rc = lib().b2g_deinterleave_device(self._h, typesize, len(plane_ptrs), interleaved_ptr, arr, n_elems, stream)
         if rc < 0:
             raise B2GError(rc, "b2g_deinterleave_device")
+
+    def interleave(self, typesize, plane_ptrs, interleaved_ptr, n_elems):
+        """Host-pointer form of interleave_device (staged through the context's device buffers, synchronous)."""
+        arr = (C.c_void_p * max(len(plane_ptrs), 1))(*plane_ptrs)
+        rc = lib().b2g_interleave(self._h, typesize, len(plane_ptrs), arr, interleaved_ptr, n_elems)
+        if rc < 0:
+            raise B2GError(rc, "b2g_interleave")
+
+    def deinterleave(self, typesize, interleaved_ptr, plane_ptrs, n_elems):
+        arr = (C.c_void_p * max(len(plane_ptrs), 1))(*plane_ptrs)
+        rc = lib().b2g_deinterleave(self._h, typesize, len(plane_ptrs), interleaved_ptr, arr, n_elems)
+        if rc < 0:
+            raise B2GError(rc, "b2g_deinterleave")
 
     @property
     def launches(self):

@@ -972,6 +972,46 @@ int b2g_deinterleave_device(b2g_ctx* c, int typesize, int nchannels, const void*
   return interleave_device(c, false, typesize, nchannels, planes, (void*)interleaved, n_elems, cuda_stream);
 }
 
+// Host-pointer form: the planes and the interleaved buffer are staged through the context's device buffers.
+static int interleave_host(b2g_ctx* c, bool to_interleaved, int typesize, int nch, void* const* planes, void* inter, int64_t n) {
+  if (!c || !planes || typesize <= 0 || typesize > 255 || nch <= 0 || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (c->pend) return B2G_ERR_FAILURE;              // d_in / d_out belong to the batch in flight
+  if (n == 0) return 0;
+  if (!inter) return B2G_ERR_INVALID_PARAM;
+  for (int k = 0; k < nch; k++)
+    if (!planes[k]) return B2G_ERR_INVALID_PARAM;
+  if (int rc = use_device(c)) return rc;
+  const size_t plane_bytes = (size_t)n * typesize, pstride = align_up(plane_bytes, 256), total = plane_bytes * nch;
+  DevBuf& d_pl = to_interleaved ? c->d_in : c->d_out;
+  DevBuf& d_il = to_interleaved ? c->d_out : c->d_in;
+  if (int rc = d_pl.ensure(pstride * nch)) return rc;
+  if (int rc = d_il.ensure(total)) return rc;
+  cudaStream_t s = c->lanes[0].stream;
+  std::vector<void*> dp((size_t)nch);
+  for (int k = 0; k < nch; k++) dp[k] = (uint8_t*)d_pl.p + (size_t)k * pstride;
+  if (to_interleaved) {
+    for (int k = 0; k < nch; k++) CU(cudaMemcpyAsync(dp[k], planes[k], plane_bytes, cudaMemcpyHostToDevice, s));
+  } else {
+    CU(cudaMemcpyAsync(d_il.p, inter, total, cudaMemcpyHostToDevice, s));
+  }
+  if (int rc = interleave_device(c, to_interleaved, typesize, nch, dp.data(), d_il.p, n, s)) return rc;
+  if (to_interleaved) {
+    CU(cudaMemcpyAsync(inter, d_il.p, total, cudaMemcpyDeviceToHost, s));
+  } else {
+    for (int k = 0; k < nch; k++) CU(cudaMemcpyAsync(planes[k], dp[k], plane_bytes, cudaMemcpyDeviceToHost, s));
+  }
+  CU(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int b2g_interleave(b2g_ctx* c, int typesize, int nchannels, const void* const* planes, void* interleaved, int64_t n_elems) {
+  return interleave_host(c, true, typesize, nchannels, (void* const*)planes, interleaved, n_elems);
+}
+
+int b2g_deinterleave(b2g_ctx* c, int typesize, int nchannels, const void* interleaved, void* const* planes, int64_t n_elems) {
+  return interleave_host(c, false, typesize, nchannels, planes, (void*)interleaved, n_elems);
+}
+
 int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }
 
 int b2g_last_kernel_ms(const b2g_ctx* c, float out_ms[2]) {

@@ -6,8 +6,8 @@ the reference throws std::invalid_argument (what pybind11 maps it to).  The work
 k_deinterleave_vec / the element kernels of csrc/b2g_interleave.cuh through b2g_interleave_device /
 b2g_deinterleave_device; there is no CPU path.
 
-Host arrays (numpy) are copied to the device and back; `interleave_device` / `deinterleave_device` take torch CUDA
-tensors and move nothing.
+Host arrays (numpy) go through b2g_interleave / b2g_deinterleave (staged to the device and back by the library);
+`interleave_device` / `deinterleave_device` take torch CUDA tensors and move nothing.
 """
 import numpy as np
 
@@ -60,39 +60,24 @@ def deinterleave_device(interleaved, channel_spans, stream=None):
                                    [s.data_ptr() for s in channel_spans], channel_spans[0].numel(), stream)
 
 
-def _as_bytes_tensor(a):
-    import torch
-    return torch.from_numpy(np.ascontiguousarray(a).reshape(-1).view(np.uint8))
-
-
 def interleave(buffer, spans):
     """Host version: `buffer` (preallocated numpy array, exactly len(spans) * spans[0].size elements) receives the
     interleaved `spans` (numpy arrays of the same dtype and size)."""
-    import torch
-    spans = [np.asarray(s) for s in spans]
+    spans = [np.ascontiguousarray(s).reshape(-1) for s in spans]
     _check_interleave(buffer.size, [s.size for s in spans])
     if any(s.dtype != buffer.dtype for s in spans):
         raise ValueError("Interleave: All spans must have the dtype of the buffer.")
     if not buffer.flags.c_contiguous:
         raise ValueError("Interleave: the buffer must be contiguous.")
-    ts, n = buffer.dtype.itemsize, spans[0].size
-    if n == 0:
-        return buffer
-    ctx = _context()
-    d_planes = [_as_bytes_tensor(s).cuda() for s in spans]
-    d_out = torch.empty(n * len(spans) * ts, dtype=torch.uint8, device="cuda")
-    torch.cuda.synchronize()
-    ctx.interleave_device(ts, [p.data_ptr() for p in d_planes], d_out.data_ptr(), n)
-    torch.cuda.synchronize()
-    buffer.reshape(-1).view(np.uint8)[:] = d_out.cpu().numpy()
+    if spans[0].size:
+        _context().interleave(buffer.dtype.itemsize, [s.ctypes.data for s in spans], buffer.ctypes.data, spans[0].size)
     return buffer
 
 
 def deinterleave(interleaved, channel_spans):
     """Host version: `channel_spans` (preallocated numpy arrays of equal size) receive the channels of
     `interleaved`; with an int instead of a list, that many new arrays are returned (image_algo.h:131-160)."""
-    import torch
-    interleaved = np.asarray(interleaved)
+    interleaved = np.ascontiguousarray(interleaved).reshape(-1)
     if isinstance(channel_spans, (int, np.integer)):
         if channel_spans <= 0 or interleaved.size % int(channel_spans):
             raise ValueError("Deinterleave: Input buffer size does not match the expected size for deinterleaving.")
@@ -101,15 +86,7 @@ def deinterleave(interleaved, channel_spans):
     _check_deinterleave(interleaved.size, [s.size for s in channel_spans])
     if any(s.dtype != interleaved.dtype or not s.flags.c_contiguous for s in channel_spans):
         raise ValueError("Deinterleave: All spans must be contiguous and have the dtype of the buffer.")
-    ts, n = interleaved.dtype.itemsize, channel_spans[0].size
-    if n == 0:
-        return channel_spans
-    ctx = _context()
-    d_in = _as_bytes_tensor(interleaved).cuda()
-    d_planes = [torch.empty(n * ts, dtype=torch.uint8, device="cuda") for _ in channel_spans]
-    torch.cuda.synchronize()
-    ctx.deinterleave_device(ts, d_in.data_ptr(), [p.data_ptr() for p in d_planes], n)
-    torch.cuda.synchronize()
-    for s, p in zip(channel_spans, d_planes):
-        s.reshape(-1).view(np.uint8)[:] = p.cpu().numpy()
+    if channel_spans[0].size:
+        _context().deinterleave(interleaved.dtype.itemsize, interleaved.ctypes.data,
+                                [s.ctypes.data for s in channel_spans], channel_spans[0].size)
     return channel_spans

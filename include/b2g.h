@@ -143,6 +143,12 @@ B2G_API int b2g_interleave_device(b2g_ctx* ctx, int typesize, int nchannels, con
                                   void* interleaved, int64_t n_elems, void* cuda_stream);
 B2G_API int b2g_deinterleave_device(b2g_ctx* ctx, int typesize, int nchannels, const void* interleaved,
                                     void* const* planes, int64_t n_elems, void* cuda_stream);
+/* The same two operations on HOST buffers (what the reference's call site holds, image.h:1880): copied to the device,
+ * run by the kernels above, copied back; returns when the result is in place.  Not while a batch is in flight. */
+B2G_API int b2g_interleave(b2g_ctx* ctx, int typesize, int nchannels, const void* const* planes, void* interleaved,
+                           int64_t n_elems);
+B2G_API int b2g_deinterleave(b2g_ctx* ctx, int typesize, int nchannels, const void* interleaved, void* const* planes,
+                             int64_t n_elems);
 
 /* Number of kernels this library has launched through `ctx` since creation (bench.py's gpu_launches). */
 B2G_API int64_t b2g_launch_count(const b2g_ctx* ctx);

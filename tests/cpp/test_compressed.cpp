@@ -6,6 +6,7 @@
 //   test/src/test_chunk_span.cpp:16-57    x() / y() from the chunk index
 //   test/src/test_image.cpp:552-858       construct from vectors, chunk == / < / > data size, modify then re-read
 //   python/test/test_channel.py:173-237   get_chunk / set_chunk round trip and the exception types
+//   test/src/util.h:40-56                 image_algo::deinterleave as the reference's test helper uses it (+ interleave back)
 // Needs a CUDA device (there is no CPU path); run by tests/test_gpu_cpp.py under -m gpu.
 #include <cstdint>
 #include <cstdio>
@@ -14,6 +15,7 @@
 #include <vector>
 
 #include "compressed/image.h"
+#include "compressed/image_algo.h"
 
 static int g_failed = 0, g_checks = 0;
 #define CHECK(cond)                                                                      \
@@ -191,6 +193,34 @@ static void test_image(size_t chunk_size)
 	CHECK(img.channelnames() == (std::vector<std::string>{ "B", "A" }));
 }
 
+template <typename T>
+static void test_image_algo(size_t nch, size_t n)
+{
+	std::vector<T> pixels(nch * n);
+	for (size_t i = 0; i < pixels.size(); ++i) pixels[i] = static_cast<T>((i * 2654435761u) >> 7);
+	std::vector<std::vector<T>> channels(nch, std::vector<T>(n));
+	ci::image_algo::deinterleave(std::span<const T>(pixels), channels);
+	bool ok = true;
+	for (size_t c = 0; c < nch && ok; ++c)
+		for (size_t i = 0; i < n; ++i)
+			if (channels[c][i] != pixels[i * nch + c]) { ok = false; break; }
+	CHECK(ok);
+	std::vector<T> back(nch * n, T{});
+	std::vector<std::span<const T>> spans;
+	for (auto& c : channels) spans.push_back(std::span<const T>(c));
+	ci::image_algo::interleave(std::span<T>(back), spans);
+	CHECK(back == pixels);
+	std::vector<T> small(nch * n - 1);
+	CHECK_THROWS_AS(ci::image_algo::interleave(std::span<T>(small), spans), std::invalid_argument);
+	std::vector<std::span<const T>> none;
+	CHECK_THROWS_AS(ci::image_algo::interleave(std::span<T>(back), none), std::invalid_argument);
+	if (nch > 1)
+	{
+		channels[1].resize(n + 1);
+		CHECK_THROWS_AS(ci::image_algo::deinterleave(std::span<const T>(pixels), channels), std::invalid_argument);
+	}
+}
+
 int main()
 {
 	if (b2g_device_count() < 1)
@@ -215,6 +245,11 @@ int main()
 	for (size_t chunk : { size_t(32 * 16 * 4), size_t(1024), size_t(768), size_t(4194304) })
 	{
 		test_image<uint8_t>(chunk); test_image<uint16_t>(chunk); test_image<float>(chunk);
+	}
+	for (size_t nch : { size_t(1), size_t(3), size_t(4), size_t(7), size_t(16) })
+	{
+		test_image_algo<uint8_t>(nch, 1000003); test_image_algo<uint16_t>(nch, 64 * 64);
+		test_image_algo<float>(nch, 12345); test_image_algo<double>(nch, 777);
 	}
 	std::printf("%d checks, %d failed\n", g_checks, g_failed);
 	return g_failed ? 1 : 0;
