@@ -279,3 +279,26 @@ class Channel:
             else:
                 out.append(c)
         return out
+
+    # ---- contiguous frame (b2frame) export / import: to_schunk() + blosc2_schunk_to_buffer (schunk.h:107-121) -------
+    def to_cframe(self):
+        """The channel's chunks as one contiguous blosc2 frame (bytes) that stock c-blosc2 opens with
+        blosc2_schunk_from_buffer; the offsets chunk is compressed on the GPU (b2frame.py)."""
+        from . import b2frame
+        enc, _ = b2frame.engine_from_context(_context(0, 5, 8, 1, DEFAULT_BLOCKSIZE, self._device))
+        return b2frame.to_cframe(self.chunks(), enc)
+
+    def set_from_cframe(self, frame):
+        """Replace the channel's chunks by those of a contiguous frame; the decompressed sizes must be the channel's."""
+        from . import b2frame
+        _, dec = b2frame.engine_from_context(_context(0, 5, 8, 1, DEFAULT_BLOCKSIZE, self._device))
+        hd, chunks = b2frame.from_cframe(frame, dec)
+        if hd["special"]:
+            raise ValueError("special-value frame entries are not supported")
+        if len(chunks) != self.num_chunks():
+            raise ValueError("frame holds %d chunks, channel has %d" % (len(chunks), self.num_chunks()))
+        for i, c in enumerate(chunks):
+            if _b2g.chunk_sizes(c)[0] != self._nbytes_of(i):
+                raise ValueError("Invalid chunk size for chunk %d" % i)
+        self._chunks = [np.array(c, dtype=np.uint8) for c in chunks]
+

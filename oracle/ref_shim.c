@@ -146,3 +146,65 @@ int ref_shuffle(int ts, int n, const void* s, void* d) { shuffle(ts, n, s, d); r
 int ref_unshuffle(int ts, int n, const void* s, void* d) { unshuffle(ts, n, s, d); return n; }
 int ref_bitshuffle(int ts, int n, const void* s, void* d) { return bitshuffle(ts, n, s, d); }
 int ref_bitunshuffle(int ts, int n, const void* s, void* d, int ver) { return bitunshuffle(ts, n, s, d, (uint8_t)ver); }
+
+/* ---- contiguous frames -------------------------------------------------------------------
+ * What compressed-image does to export a channel: schunk::to_schunk() (compressed/blosc2/schunk.h:107-121: a default
+ * schunk from wrapper.h:301-310, every chunk appended with copy) followed by blosc2_schunk_to_buffer (schunk.c:357). */
+int64_t ref_chunks_to_cframe(int n, const void* const* chunks, void* dst, int64_t cap) {
+  blosc2_init();
+  blosc2_cparams cp = BLOSC2_CPARAMS_DEFAULTS;
+  blosc2_dparams dp = BLOSC2_DPARAMS_DEFAULTS;
+  blosc2_storage st = BLOSC2_STORAGE_DEFAULTS;
+  st.cparams = &cp;
+  st.dparams = &dp;
+  blosc2_schunk* sc = blosc2_schunk_new(&st);
+  if (!sc) return -1;
+  for (int i = 0; i < n; i++) {
+    if (blosc2_schunk_append_chunk(sc, (uint8_t*)chunks[i], true) < 0) { blosc2_schunk_free(sc); return -2; }
+  }
+  uint8_t* cframe = NULL;
+  bool needs_free = false;
+  int64_t len = blosc2_schunk_to_buffer(sc, &cframe, &needs_free);
+  if (len > 0 && len <= cap) memcpy(dst, cframe, (size_t)len);
+  else if (len > cap) len = -3;
+  if (needs_free) free(cframe);
+  blosc2_schunk_free(sc);
+  return len;
+}
+
+/* blosc2_schunk_from_buffer (schunk.c:676): out[0] nchunks, out[1] nbytes, out[2] cbytes, out[3] typesize,
+ * out[4] chunksize, out[5] blocksize. */
+int ref_cframe_info(const void* cframe, int64_t len, int64_t* out) {
+  blosc2_init();
+  blosc2_schunk* sc = blosc2_schunk_from_buffer((uint8_t*)cframe, len, false);
+  if (!sc) return -1;
+  out[0] = sc->nchunks; out[1] = sc->nbytes; out[2] = sc->cbytes; out[3] = sc->typesize; out[4] = sc->chunksize;
+  out[5] = sc->blocksize;
+  blosc2_schunk_free(sc);
+  return 0;
+}
+
+/* chunk i of a frame, still compressed (blosc2_schunk_get_chunk) -> cbytes, or negative */
+int ref_cframe_get_chunk(const void* cframe, int64_t len, int64_t i, void* dst, int32_t cap) {
+  blosc2_init();
+  blosc2_schunk* sc = blosc2_schunk_from_buffer((uint8_t*)cframe, len, false);
+  if (!sc) return -1;
+  uint8_t* chunk = NULL;
+  bool needs_free = false;
+  int cb = blosc2_schunk_get_chunk(sc, i, &chunk, &needs_free);
+  if (cb > 0 && cb <= cap) memcpy(dst, chunk, (size_t)cb);
+  else if (cb > cap) cb = -3;
+  if (needs_free) free(chunk);
+  blosc2_schunk_free(sc);
+  return cb;
+}
+
+/* chunk i of a frame, decompressed by the reference (blosc2_schunk_decompress_chunk) -> nbytes, or negative */
+int ref_cframe_decompress_chunk(const void* cframe, int64_t len, int64_t i, void* dst, int32_t cap) {
+  blosc2_init();
+  blosc2_schunk* sc = blosc2_schunk_from_buffer((uint8_t*)cframe, len, false);
+  if (!sc) return -1;
+  int nb = blosc2_schunk_decompress_chunk(sc, i, dst, cap);
+  blosc2_schunk_free(sc);
+  return nb;
+}
