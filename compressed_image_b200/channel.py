@@ -57,6 +57,40 @@ def align_chunk_to_scanlines_bytes(width, chunk_size, itemsize):
     return lines * width * itemsize
 
 
+_iter_free = {}
+
+
+def _iter_context(key):
+    """A context nobody else is using, for the lifetime of one channel iterator (returned by _iter_release)."""
+    free = _iter_free.setdefault(key, [])
+    return free.pop() if free else _b2g.Context(*key)
+
+
+def _iter_release(key, ctx):
+    _iter_free.setdefault(key, []).append(ctx)
+
+
+_pin_free = {}
+
+
+def _pinned(nbytes):
+    """Page-locked host bytes (so the iterator's copies really are asynchronous), from a free list by size: pinning
+    costs about a millisecond per buffer, an iterator needs five.  Plain numpy memory without torch."""
+    nbytes = int(nbytes)
+    free = _pin_free.get(nbytes)
+    if free:
+        return free.pop()
+    try:
+        import torch
+        return torch.empty(nbytes, dtype=torch.uint8, pin_memory=True).numpy()
+    except Exception:
+        return np.empty(nbytes, dtype=np.uint8)
+
+
+def _pinned_release(buf):
+    _pin_free.setdefault(int(buf.nbytes), []).append(buf.reshape(-1).view(np.uint8))
+
+
 class _Lazy:
     """A lazy fill-value chunk (blosc2/lazyschunk.h:47-105): nbytes of one repeated element, never compressed."""
     __slots__ = ("value", "nbytes")
@@ -259,16 +293,90 @@ class Channel:
     # ---- chunk iteration (iterators/iterator.h:97-141: decompress -> user modifies -> recompress) --------------
     def __iter__(self):
         """Yields each chunk as a writable 1-D array; modifications are recompressed when the iterator advances
-        (and at exhaustion), like compressed::channel_iterator."""
-        for i in range(len(self._chunks)):
-            buf = self.get_chunk(i)
-            before = buf.copy()
+        (and at exhaustion), like compressed::channel_iterator.
+
+        Double-buffered: while the caller works on chunk i, chunk i + 1 is already being decompressed and the
+        modified chunk i - 1 is being compressed (b2g_decompress_batch_async / b2g_compress_batch_async on two contexts
+        taken from a free list for the lifetime of the iterator, so that zip() over several channels and get_chunk()
+        calls from inside the loop never meet a context with a batch in flight).  Three buffers rotate: the one the
+        caller holds, the one being filled and the one being read by the compressor."""
+        n = len(self._chunks)
+        if n == 0:
+            return
+        key = (self._codec.blosc2_id, self._level, self._dtype.itemsize, self._filter, self._block_size, self._device)
+        dctx, cctx = _iter_context(key), _iter_context(key)
+        itemsize = self._dtype.itemsize
+        nb0 = self._nbytes_of(0)
+        bufs = [_pinned(nb0).view(self._dtype) for _ in range(min(n, 3))]
+        before_buf = np.empty(nb0, dtype=np.uint8)                 # reused: no fresh pages per chunk
+        dsts = [_pinned(nb0 + _b2g.MAX_OVERHEAD) for _ in range(2)]
+        fetch = None        # (index, view, batch or None, chunk kept alive)
+        pending = None      # (index, batch, dst, src kept alive)
+
+        def start_fetch(i):
+            view = bufs[i % len(bufs)][:self._nbytes_of(i) // itemsize]
+            c = self._chunks[i]
+            if isinstance(c, _Lazy):
+                view[:] = c.value
+                return (i, view, None, None)
+            c = np.ascontiguousarray(c)
+            b = dctx.make_batch([c.ctypes.data], [view.ctypes.data], [int(c.size)], [int(view.nbytes)])
+            dctx.decompress_batch_async(b)
+            return (i, view, b, c)
+
+        def finish_fetch(f):
+            if f[2] is not None:
+                dctx.wait()
+                if f[2][0].status < 0:
+                    raise _b2g.B2GError(f[2][0].status, "decompress chunk %d" % f[0])
+            return f[1]
+
+        def collect():
+            nonlocal pending
+            if pending is not None:
+                i, b, dst, _src = pending
+                pending = None
+                cctx.wait()
+                if b[0].status < 0:
+                    raise _b2g.B2GError(b[0].status, "compress chunk %d" % i)
+                self._chunks[i] = dst[:b[0].out_bytes].copy()
+
+        def start_compress(i, view):
+            nonlocal pending
+            collect()
+            src = view.view(np.uint8)
+            dst = dsts[i & 1]                                       # the other one may still be held by `pending`
+            b = cctx.make_batch([src.ctypes.data], [dst.ctypes.data], [int(src.size)], [int(dst.size)])
+            cctx.compress_batch_async(b)
+            pending = (i, b, dst, view)
+
+        try:
+            fetch = start_fetch(0)
+            for i in range(n):
+                buf = finish_fetch(fetch)
+                fetch = None
+                if i + 1 < n:
+                    if len(bufs) < 3 or (pending is not None and pending[0] <= i - 2):
+                        collect()                       # the buffer about to be refilled must have been read
+                    fetch = start_fetch(i + 1)
+                before = before_buf[:buf.nbytes]
+                np.copyto(before, buf.view(np.uint8))
+                try:
+                    yield buf
+                finally:    # also runs when the iteration is abandoned (zip over channels stops at the first
+                    # exhausted iterator): the reference flushes the last chunk in ~channel_iterator (iterator.h:72-93)
+                    if not np.array_equal(before, buf.view(np.uint8)):
+                        start_compress(i, buf)
+        finally:
             try:
-                yield buf
-            finally:   # also runs when the iteration is abandoned (zip over channels stops at the first exhausted
-                # iterator): the reference flushes the last chunk in ~channel_iterator (iterator.h:72-93)
-                if not np.array_equal(before.view(np.uint8), buf.view(np.uint8)):
-                    self.set_chunk(i, buf)
+                if fetch is not None:
+                    finish_fetch(fetch)
+                collect()
+            finally:
+                _iter_release(key, dctx)
+                _iter_release(key, cctx)
+                for b in bufs + dsts:
+                    _pinned_release(b)
 
     def chunks(self):
         """The stored chunk bytes (numpy uint8 arrays; lazy chunks are materialised as blosc2 special chunks)."""

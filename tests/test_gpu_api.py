@@ -235,3 +235,54 @@ def test_image_zip_modify_reread():
         b[:] = g + 1.0
     out = img.get_decompressed()
     assert np.all(out[0] == 1.0) and np.all(out[1] == 2.0) and np.all(out[2] == 3.0)
+
+
+def test_iterator_double_buffered_many_chunks():
+    """The double-buffered iterator over 23 chunks (last one short): every third chunk modified, get_chunk() and
+    set_chunk() of OTHER chunks from inside the loop, chunk views rotate over three buffers; then an abandoned
+    iteration flushes its last modification, and lazy channels iterate as fills."""
+    import compressed_image_b200 as c
+    rng = np.random.default_rng(3)
+    w, h = 256, 23 * 16 - 5
+    data = (np.cumsum(rng.integers(0, 3, size=(h, w)), axis=1) & 0x3ff).astype(np.uint16)
+    ch = c.Channel(data, w, h, chunk_size=16 * w * 2)
+    assert ch.num_chunks() == 23
+    flat = data.reshape(-1).copy()
+    per = 16 * w
+    seen = 0
+    for i, chunk in enumerate(ch):
+        assert np.array_equal(chunk, flat[i * per:i * per + chunk.size]), i
+        if i % 3 == 0:
+            chunk += 7
+            flat[i * per:i * per + chunk.size] += 7
+        if i == 5:                                            # other chunks through the channel's own context
+            assert np.array_equal(ch.get_chunk(1), flat[per:2 * per])
+            ch.set_chunk(20, np.full(per, 9, np.uint16))
+            flat[20 * per:21 * per] = 9
+        seen += 1
+    assert seen == 23
+    assert np.array_equal(np.asarray(ch.get_decompressed()).reshape(-1), flat)
+    for i, chunk in enumerate(ch):                            # abandoned after a modification
+        chunk[:] = 1
+        flat[i * per:i * per + chunk.size] = 1
+        if i == 2:
+            break
+    del chunk
+    import gc
+    gc.collect()
+    assert np.array_equal(np.asarray(ch.get_decompressed()).reshape(-1), flat)
+    lazy = c.Channel.full(np.uint16, 5, w, h, chunk_size=16 * w * 2)
+    total = 0
+    for i, chunk in enumerate(lazy):
+        assert (chunk == 5).all()
+        if i == 4:
+            chunk[0] = 6
+        total += chunk.size
+    assert total == w * h
+    out = np.asarray(lazy.get_decompressed()).reshape(-1)
+    assert out[4 * per] == 6 and (np.delete(out, 4 * per) == 5).all()
+    a, b = c.Channel(data, w, h, chunk_size=16 * w * 2), c.Channel(data + 1, w, h, chunk_size=16 * w * 2)
+    for x, y in zip(a, b):                                    # two iterators of identical parameters at once
+        assert np.array_equal(x + 1, y)
+        x[:] = y
+    assert np.array_equal(np.asarray(a.get_decompressed()), np.asarray(b.get_decompressed()))

@@ -1,1 +1,2 @@
-(timeout 600 python -m pytest tests/test_b2frame.py tests/test_gpu_interleave.py -m gpu -x -q 2>&1 | tail -15)
+timeout 300 python tools/bench_iterator.py 2>&1 | tail -3
+(timeout 600 python -m pytest tests/test_gpu_api.py -m gpu -x -q 2>&1 | tail -3)
