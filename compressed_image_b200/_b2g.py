@@ -81,7 +81,7 @@ def lib():
 EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
            "b2g_decompress_batch_async", "b2g_compress_batch_device",
            "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
-           "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_launch_count",
+           "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_clone", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 
 

@@ -1012,6 +1012,13 @@ int b2g_deinterleave(b2g_ctx* c, int typesize, int nchannels, const void* interl
   return interleave_host(c, false, typesize, nchannels, planes, (void*)interleaved, n_elems);
 }
 
+b2g_ctx* b2g_clone(const b2g_ctx* c) {
+  if (!c) return nullptr;
+  b2g_params p = c->p;
+  p.device = c->dev;
+  return b2g_create(&p);
+}
+
 int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }
 
 int b2g_last_kernel_ms(const b2g_ctx* c, float out_ms[2]) {

@@ -150,6 +150,11 @@ B2G_API int b2g_interleave(b2g_ctx* ctx, int typesize, int nchannels, const void
 B2G_API int b2g_deinterleave(b2g_ctx* ctx, int typesize, int nchannels, const void* interleaved, void* const* planes,
                              int64_t n_elems);
 
+/* A new context with the parameters of `ctx` (its own streams and work buffers): what an iterator takes so that its
+ * batches in flight never collide with calls on the channel's own contexts (iterators/iterator.h:209-210 shares them,
+ * which is safe there because blosc2 contexts never have work in flight between calls). */
+B2G_API b2g_ctx* b2g_clone(const b2g_ctx* ctx);
+
 /* Number of kernels this library has launched through `ctx` since creation (bench.py's gpu_launches). */
 B2G_API int64_t b2g_launch_count(const b2g_ctx* ctx);
 /* Milliseconds the last batch's kernels took on the device (CUDA events on the launching stream), split by

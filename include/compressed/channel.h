@@ -49,6 +49,11 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 	/// Forward iterator over the chunks of a channel (iterators/iterator.h:97-141): dereferencing decompresses the
 	/// current chunk into a buffer owned by the iterator and returns a chunk_span over it; advancing (and destroying
 	/// the iterator) compresses the buffer back into the channel.
+	///
+	/// Double-buffered: while the caller works on chunk i, chunk i + 1 is already being decompressed
+	/// (b2g_decompress_batch_async) and chunk i - 1 is being compressed (b2g_compress_batch_async), on two contexts
+	/// cloned from the channel's (b2g_clone) so that calls on the channel from inside the loop never meet a context with
+	/// a batch in flight.  Three buffers rotate; a chunk_span stays valid until the iterator has advanced twice.
 	template <typename T>
 	struct channel_iterator
 	{
@@ -67,9 +72,17 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 				throw std::runtime_error("passed zero width or height to iterator which is not valid");
 			}
 		}
+		/// A copy refers to the same position but starts with nothing loaded and nothing in flight.
 		channel_iterator(const channel_iterator& other)
 			: m_Schunk(other.m_Schunk), m_Cctx(other.m_Cctx), m_Dctx(other.m_Dctx), m_ChunkIndex(other.m_ChunkIndex),
 			  m_Width(other.m_Width), m_Height(other.m_Height) {}
+		channel_iterator(channel_iterator&& other) noexcept
+			: m_Schunk(other.m_Schunk), m_Cctx(other.m_Cctx), m_Dctx(other.m_Dctx), m_ChunkIndex(other.m_ChunkIndex),
+			  m_Width(other.m_Width), m_Height(other.m_Height), m_Pipe(std::move(other.m_Pipe)), m_Loaded(other.m_Loaded),
+			  m_Cur(other.m_Cur)
+		{
+			other.m_Loaded = npos;
+		}
 		channel_iterator& operator=(const channel_iterator& other)
 		{
 			if (this != &other)
@@ -93,12 +106,24 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 			}
 			if (m_Loaded != m_ChunkIndex)
 			{
-				flush();
-				m_Buffer.resize(m_Schunk->chunk_elements(m_ChunkIndex));
-				m_Schunk->chunk(m_Dctx, std::span<T>(m_Buffer), m_ChunkIndex);
+				pipeline& p = pipe();
+				start_compress();                                    // chunk m_Loaded leaves while the next one is fetched
+				if (p.fetch_index == m_ChunkIndex)
+				{
+					wait_fetch();
+					m_Cur = p.fetch_buf;
+				}
+				else                                                 // first dereference, or a jump
+				{
+					wait_fetch();
+					m_Cur = free_buffer(npos);
+					p.buf[m_Cur].resize(m_Schunk->chunk_elements(m_ChunkIndex));
+					m_Schunk->chunk(p.dctx.get(), std::span<T>(p.buf[m_Cur]), m_ChunkIndex);
+				}
 				m_Loaded = m_ChunkIndex;
+				start_fetch(m_ChunkIndex + 1);
 			}
-			return value_type(std::span<T>(m_Buffer), m_Width, m_Height, m_ChunkIndex, m_Schunk->chunk_bytes());
+			return value_type(std::span<T>(m_Pipe->buf[m_Cur]), m_Width, m_Height, m_ChunkIndex, m_Schunk->chunk_bytes());
 		}
 
 		channel_iterator& operator++()
@@ -119,21 +144,114 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 		std::size_t chunk_index() const noexcept { return m_ChunkIndex; }
 
 	private:
-		void flush()
+		static constexpr std::size_t npos = static_cast<std::size_t>(-1);
+
+		/// Everything a batch in flight points at lives here, on the heap, so that moving the iterator moves nothing.
+		struct pipeline
 		{
-			if (m_Schunk && m_Loaded != npos)
+			blosc2::context_ptr dctx, cctx;
+			std::vector<T> buf[3];
+			std::vector<std::byte> cbuf;
+			b2g_chunk fetch_job{}, comp_job{};
+			std::size_t fetch_index = npos, comp_index = npos;
+			std::size_t fetch_buf = 0, comp_buf = 0;
+		};
+
+		pipeline& pipe()
+		{
+			if (!m_Pipe)
 			{
-				m_Schunk->set_chunk(m_Cctx, std::span<const T>(m_Buffer.data(), m_Buffer.size()), m_Loaded);
-				m_Loaded = npos;
+				m_Pipe = std::make_unique<pipeline>();
+				m_Pipe->dctx = blosc2::context_ptr(b2g_clone(m_Dctx));
+				m_Pipe->cctx = blosc2::context_ptr(b2g_clone(m_Cctx));
+				if (!m_Pipe->dctx || !m_Pipe->cctx)
+				{
+					m_Pipe.reset();
+					throw std::runtime_error(std::string("Unable to create the iterator's b2g contexts: ") + b2g_last_error());
+				}
 			}
+			return *m_Pipe;
 		}
 
-		static constexpr std::size_t npos = static_cast<std::size_t>(-1);
+		/// A buffer that is neither the loaded one, nor being compressed, nor `other`.
+		std::size_t free_buffer(std::size_t other) const
+		{
+			for (std::size_t k = 0; k < 3; ++k)
+			{
+				if (k == other) continue;
+				if (m_Loaded != npos && k == m_Cur) continue;
+				if (m_Pipe->comp_index != npos && k == m_Pipe->comp_buf) continue;
+				return k;
+			}
+			return 0;  // unreachable: at most two of the three are taken
+		}
+
+		void start_fetch(std::size_t index)
+		{
+			pipeline& p = *m_Pipe;
+			if (index >= m_Schunk->num_chunks() || m_Schunk->is_lazy(index)) return;   // lazy chunks are fills: nothing to overlap
+			const std::size_t k = free_buffer(npos);
+			p.buf[k].resize(m_Schunk->chunk_elements(index));
+			const auto chunk = m_Schunk->chunk_data(index);
+			p.fetch_job = b2g_chunk{ chunk.data(), p.buf[k].data(), static_cast<int32_t>(chunk.size()),
+				static_cast<int32_t>(p.buf[k].size() * sizeof(T)), 0, 0 };
+			const int rc = b2g_decompress_batch_async(p.dctx.get(), &p.fetch_job, 1, nullptr);
+			if (rc < 0) blosc2::detail::throw_status("Error while decompressing blosc2 chunk", rc);
+			p.fetch_index = index;
+			p.fetch_buf = k;
+		}
+
+		void wait_fetch()
+		{
+			pipeline& p = *m_Pipe;
+			if (p.fetch_index == npos) return;
+			p.fetch_index = npos;
+			const int rc = b2g_wait(p.dctx.get());
+			if (rc < 0 || p.fetch_job.status < 0)
+				blosc2::detail::throw_status("Error while decompressing blosc2 chunk", rc < 0 ? rc : p.fetch_job.status);
+		}
+
+		void start_compress()
+		{
+			if (!m_Pipe || m_Loaded == npos) return;
+			pipeline& p = *m_Pipe;
+			wait_compress();
+			const std::size_t bytes = p.buf[m_Cur].size() * sizeof(T);
+			p.cbuf.resize(blosc2::min_compressed_size(bytes));
+			p.comp_job = b2g_chunk{ p.buf[m_Cur].data(), p.cbuf.data(), static_cast<int32_t>(bytes),
+				static_cast<int32_t>(p.cbuf.size()), 0, 0 };
+			const int rc = b2g_compress_batch_async(p.cctx.get(), &p.comp_job, 1, nullptr);
+			if (rc < 0) blosc2::detail::throw_status("Error while compressing blosc2 chunk", rc);
+			p.comp_index = m_Loaded;
+			p.comp_buf = m_Cur;
+			m_Loaded = npos;
+		}
+
+		void wait_compress()
+		{
+			pipeline& p = *m_Pipe;
+			if (p.comp_index == npos) return;
+			const std::size_t index = p.comp_index;
+			p.comp_index = npos;
+			const int rc = b2g_wait(p.cctx.get());
+			if (rc < 0 || p.comp_job.status < 0)
+				blosc2::detail::throw_status("Error while compressing blosc2 chunk", rc < 0 ? rc : p.comp_job.status);
+			m_Schunk->set_chunk(std::vector<std::byte>(p.cbuf.begin(), p.cbuf.begin() + p.comp_job.out_bytes), index);
+		}
+
+		void flush()
+		{
+			if (!m_Pipe) return;
+			try { wait_fetch(); } catch (...) {}     // a prefetch nobody will look at
+			start_compress();
+			wait_compress();
+		}
+
 		blosc2::schunk<T>* m_Schunk = nullptr;
 		blosc2::context_raw_ptr m_Cctx = nullptr, m_Dctx = nullptr;
 		std::size_t m_ChunkIndex = 0, m_Width = 1, m_Height = 1;
-		std::vector<T> m_Buffer;
-		std::size_t m_Loaded = npos;
+		std::unique_ptr<pipeline> m_Pipe;
+		std::size_t m_Loaded = npos, m_Cur = 0;
 	};
 
 	template <typename T>

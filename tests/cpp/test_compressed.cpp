@@ -193,6 +193,45 @@ static void test_image(size_t chunk_size)
 	CHECK(img.channelnames() == (std::vector<std::string>{ "B", "A" }));
 }
 
+// The double-buffered iterator over 23 chunks (the last one short): contents, every third chunk modified, calls on the
+// channel's own contexts from inside the loop, an abandoned iteration flushing its last chunk.
+static void test_iterator_pipeline()
+{
+	const size_t w = 256, h = 23 * 16 - 5, per = 16 * w;
+	std::vector<uint16_t> flat(w * h);
+	for (size_t i = 0; i < flat.size(); ++i) flat[i] = static_cast<uint16_t>((i * 13 + (i >> 9)) & 0x3ff);
+	ci::channel<uint16_t> ch(std::span<const uint16_t>(flat), w, h, ci::enums::codec::lz4, 9, 32768, per * sizeof(uint16_t));
+	CHECK(ch.num_chunks() == 23);
+	size_t i = 0;
+	bool ok = true;
+	for (auto chunk : ch)
+	{
+		for (size_t k = 0; k < chunk.size() && ok; ++k) ok = chunk[k] == flat[i * per + k];
+		if (i % 3 == 0)
+			for (size_t k = 0; k < chunk.size(); ++k) { chunk[k] = static_cast<uint16_t>(chunk[k] + 7); flat[i * per + k] = static_cast<uint16_t>(flat[i * per + k] + 7); }
+		if (i == 5)
+		{
+			std::vector<uint16_t> tmp(per);
+			ch.get_chunk(std::span<uint16_t>(tmp), 1);
+			for (size_t k = 0; k < per && ok; ++k) ok = tmp[k] == flat[per + k];
+			std::fill(tmp.begin(), tmp.end(), uint16_t{ 9 });
+			ch.set_chunk(std::span<uint16_t>(tmp), 20);
+			std::fill(flat.begin() + 20 * per, flat.begin() + 21 * per, uint16_t{ 9 });
+		}
+		++i;
+	}
+	CHECK(ok);
+	CHECK(i == 23);
+	CHECK(ch.get_decompressed() == flat);
+	i = 0;
+	for (auto chunk : ch)
+	{
+		for (size_t k = 0; k < chunk.size(); ++k) { chunk[k] = 1; flat[i * per + k] = 1; }
+		if (++i == 3) break;
+	}
+	CHECK(ch.get_decompressed() == flat);
+}
+
 template <typename T>
 static void test_image_algo(size_t nch, size_t n)
 {
@@ -246,6 +285,7 @@ int main()
 	{
 		test_image<uint8_t>(chunk); test_image<uint16_t>(chunk); test_image<float>(chunk);
 	}
+	test_iterator_pipeline();
 	for (size_t nch : { size_t(1), size_t(3), size_t(4), size_t(7), size_t(16) })
 	{
 		test_image_algo<uint8_t>(nch, 1000003); test_image_algo<uint16_t>(nch, 64 * 64);

@@ -1,2 +1,2 @@
-timeout 300 python tools/bench_iterator.py 2>&1 | tail -3
-(timeout 600 python -m pytest tests/test_gpu_api.py -m gpu -x -q 2>&1 | tail -3)
+./tests/cpp/test_compressed 2>&1 | tail -8
+(timeout 600 python -m pytest tests/test_cpp_host.py tests/test_abi.py -m gpu -x -q 2>&1 | tail -3)
