@@ -67,10 +67,6 @@ struct HostBuf {  // pinned
 };
 
 constexpr int kMaxSmemWindow = 160 * 1024;  // larger blocks decode through the global slab
-// B2G_TWO_PHASE=1 (read when a context is created) decodes lz4 / blosclz streams in two phases: k_parse (one lane per
-// stream -> sequence records) + record replay in k_decode.  Off by default: on the bench image the replay (0.62 ms) plus
-// the parse (0.30 ms) is slower than the one-pass warp decoder (0.71 ms); see DESIGN.md section 4.
-bool env_two_phase() { const char* e = getenv("B2G_TWO_PHASE"); return e && e[0] == '1'; }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -85,15 +81,13 @@ struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
-  cudaEvent_t ev_mid = nullptr;                      // between k_parse and k_decode (B2G_TIMING=1)
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_itab, d_rec, d_stage, d_pair;
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_stage, d_pair;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
   void release() {
-    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_itab, &d_rec, &d_stage, &d_pair}) b->release();
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_stage, &d_pair}) b->release();
     for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     if (res_ready) cudaEventDestroy(res_ready);
-    if (ev_mid) cudaEventDestroy(ev_mid);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -110,7 +104,6 @@ struct b2g_ctx {
   int win_bytes = 32768;   // shared-memory window (standalone filters)
   int max_grid_warps = 0;  // most worker warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
-  bool two_phase = false;  // B2G_TWO_PHASE=1 at creation
   bool pair_planes = true; // B2G_PAIR_PLANES=0 at creation: every plane scatters its own bytes
   // device + pinned work buffers
   DevBuf d_in, d_out;      // staging of the host-pointer calls (chunks / raw data of a whole batch)
@@ -204,7 +197,7 @@ struct DecGeom {
 int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g, bool any_blosclz = true) {
   if (stream_bytes > 96 * 1024) stream_bytes = 16 * 1024;  // such streams decode through the global slab anyway
   g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1), any_blosclz ? kFmtBlosclz : kFmtLz4), 1024);
-  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : (c->two_phase ? kSeqGroupSmem : 0));  // + replay scratch
+  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : 0);
   int best = 0;
   g.warps = 1;
   for (int w = 1; w <= 16; w++) {
@@ -247,19 +240,13 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     if (int rc = L.h_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
     h_res = (DResult*)L.h_res.p;
   }
-  // two-phase decode (k_parse -> records -> k_decode): one ItemRec per stream item, 8-byte sequence records in regions
-  // of cbytes / 2 + 2 per chunk (k_plan_decode lays them out; chunks that do not fit fall back to the one-pass decoder)
-  int64_t itab_cap = 0, rec_cap = 0;
+  // upper bound of the batch's stream items (sizes the plane-pairing mailboxes)
+  int64_t item_cap = 0;
   const int hint_block = std::max(std::min(c->p.blocksize, c->blocksize), 1024);
-  for (int i = 0; i < n; i++) {
-    const int64_t cap = std::max(h_desc[i].dst_cap, 0);
-    itab_cap += (cap / hint_block + 2) * kMaxStreams;
-    rec_cap += std::min<int64_t>(std::max(h_desc[i].src_bytes, 0), cap + B2G_MAX_OVERHEAD) / 2 + 2;
-  }
-  itab_cap = std::min<int64_t>(itab_cap, (int64_t)1 << 27);
+  for (int i = 0; i < n; i++) item_cap += ((int64_t)std::max(h_desc[i].dst_cap, 0) / hint_block + 2) * kMaxStreams;
   // plane pairing (DecodeArgs::stage): a ring of staging slots, one flag per slot, a mailbox and a counter per item for
   // each of the two kernels; everything but the slots is zeroed per batch
-  const int64_t pair_cap = c->pair_planes ? std::min<int64_t>(itab_cap, (int64_t)1 << 24) : 0;
+  const int64_t pair_cap = c->pair_planes ? std::min<int64_t>(item_cap, (int64_t)1 << 24) : 0;
   const int nslots = 2048;
   const size_t slot_bytes = (size_t)g.wcap;
   const size_t pair_ints = (size_t)nslots + 4 * (size_t)pair_cap;
@@ -268,9 +255,6 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     if (int rc = L.d_pair.ensure(sizeof(int32_t) * pair_ints)) return rc;
     CU(cudaMemsetAsync(L.d_pair.p, 0, sizeof(int32_t) * pair_ints, s));
   }
-  if (!c->two_phase) itab_cap = rec_cap = 0;
-  if (int rc = L.d_itab.ensure(sizeof(ItemRec) * (size_t)itab_cap + 16)) return rc;
-  if (int rc = L.d_rec.ensure(sizeof(uint2) * (size_t)rec_cap + 16)) return rc;
   CU(cudaMemcpyAsync(L.d_chunks.p, h_desc, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
   CU(cudaEventRecord(L.ev[0], s));
   PlanArgs pa;
@@ -282,7 +266,6 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   pa.n = n;
   pa.max_block = std::max(c->blocksize, c->p.blocksize);
   pa.zstd_ok = want_zstd ? 1 : 0;
-  pa.rec_cap = rec_cap;
   k_plan_decode<<<1, kPlanThreads, kPlanSmemBytes, s>>>(pa);
   c->launches++;
   CU(cudaEventRecord(L.ev[1], s));
@@ -297,9 +280,6 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.wstride = g.wstride;
   da.slab = (uint8_t*)L.d_slab.p;
   da.slab_stride = (int64_t)slab_stride(c);
-  da.itab = itab_cap > 0 ? (ItemRec*)L.d_itab.p : nullptr;
-  da.itab_cap = (int32_t)itab_cap;
-  da.rec = (uint2*)L.d_rec.p;
   da.stage = pair_cap > 0 ? (uint8_t*)L.d_stage.p : nullptr;
   da.slotflag = (int32_t*)L.d_pair.p;
   da.mail = da.slotflag + nslots;
@@ -307,11 +287,6 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.nslots = nslots;
   da.slot_bytes = (int32_t)slot_bytes;
   da.pair_cap = (int32_t)pair_cap;
-  if (itab_cap > 0) {
-    k_parse<<<c->sms * 6, kParseThreads, kParseSmemBytes, s>>>(da);
-    c->launches++;
-  }
-  CU(cudaEventRecord(L.ev_mid, s));
   k_decode<false><<<g.grid, 32 * g.warps, g.smem, s>>>(da);
   c->launches++;
   if (want_zstd) {
@@ -440,15 +415,11 @@ int finish(b2g_ctx* c, Lane& L, b2g_chunk* chunks, int n) {
   if (cudaEventElapsedTime(&a, L.ev[0], L.ev[1]) == cudaSuccess) c->last_ms[0] += a;
   if (cudaEventElapsedTime(&b, L.ev[1], L.ev[2]) == cudaSuccess) c->last_ms[1] += b;
   static const bool timing = [] { const char* e = getenv("B2G_TIMING"); return e && e[0] == '1'; }();
-  if (timing) {  // developer switch: the parse / replay split of a decode batch
-    float m = 0;
-    if (cudaEventElapsedTime(&m, L.ev[1], L.ev_mid) == cudaSuccess && m > 0)
-    {
-      BatchCtl ctl[2];
-      cudaMemcpy(ctl, L.d_ctl.p, sizeof(ctl), cudaMemcpyDeviceToHost);
-      fprintf(stderr, "b2g timing: plan %.3f ms, first kernel %.3f ms, rest %.3f ms; items %d, replayed %d, blocks paired %d\n",
-              a, m, b - m, ctl[0].total_items, ctl[0].replayed, ctl[0].paired);
-    }
+  if (timing) {  // developer switch
+    BatchCtl ctl[2];
+    cudaMemcpy(ctl, L.d_ctl.p, sizeof(ctl), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "b2g timing: plan %.3f ms, kernels %.3f ms; items %d, blocks paired %d\n", a, b, ctl[0].total_items,
+            ctl[0].paired);
   }
   return 0;
 }
@@ -575,7 +546,6 @@ b2g_ctx* b2g_create(const b2g_params* params) {
   }
   b2g_ctx* c = new b2g_ctx();
   c->p = *params;
-  c->two_phase = env_two_phase();
   { const char* e = getenv("B2G_PAIR_PLANES"); c->pair_planes = !(e && e[0] == '0'); }
   if (c->p.typesize == 0) c->p.typesize = 1;
   if (c->p.blocksize <= 0) c->p.blocksize = 32768;
@@ -589,7 +559,6 @@ b2g_ctx* b2g_create(const b2g_params* params) {
     ok = !cuda_fail(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking), "cudaStreamCreate");
     for (int i = 0; ok && i < 3; i++) ok = !cuda_fail(cudaEventCreate(&L.ev[i]), "cudaEventCreate");
     if (ok) ok = !cuda_fail(cudaEventCreateWithFlags(&L.res_ready, cudaEventDisableTiming), "cudaEventCreate");
-    if (ok) ok = !cuda_fail(cudaEventCreate(&L.ev_mid), "cudaEventCreate");
   }
   c->stream_hint = c->p.blocksize / plan_nstreams(c->p.codec, c->p.clevel, c->p.filter, c->p.typesize, c->p.blocksize);
   if (ok) ok = set_geometry(c, c->p.blocksize) == 0;

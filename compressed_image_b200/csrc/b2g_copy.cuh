@@ -21,6 +21,21 @@ __device__ __forceinline__ uint4 ld16_unaligned(const uint8_t* s) {
   return v;
 }
 
+// 16 bytes global -> shared without a register in between (LDGSTS); both addresses 16-byte aligned.
+__device__ __forceinline__ void async_copy16(void* smem_dst, const void* gmem_src) {
+#ifdef B2G_SIM
+  *(uint4*)smem_dst = *(const uint4*)gmem_src;
+#else
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+#endif
+}
+__device__ __forceinline__ void async_copy_wait() {
+#ifndef B2G_SIM
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
 // dst[0..n) = src[0..n); the ranges must not overlap.
 __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, int n, int tid, int nthr) {
   if (n <= 0) return;

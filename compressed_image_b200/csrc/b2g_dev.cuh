@@ -45,8 +45,6 @@ struct DInfo {
   int32_t nitems;        // work items: streams (blocks for special / memcpyed chunks); 0 for empty / failed chunks
   int32_t vts;           // special "repeated value" chunks: size of the value (cbytes - 32)
   int32_t nstreams;      // streams a full block is stored as (typesize when split, else 1)
-  int32_t rec_div;       // sequence records: a stream's region starts at rec_base + payload_pos / rec_div
-  long long rec_base;    // first sequence record of this chunk's region (k_parse -> k_decode), -1 = no records
   uint8_t version, flags, typesize, filter, fmt, dont_split, special, memcpyed, hdr, cls, serial, pad;
 };
 
@@ -85,11 +83,9 @@ struct CParams {
 struct BatchCtl {
   int32_t total_items;   // written by the plan kernel (decode) or the host (compress)
   int32_t ticket;        // dynamic work distribution
-  int32_t parse_ticket;  // k_parse's own ticket (32 items per draw)
-  int32_t replayed;      // items decoded by record replay (statistics: B2G_TIMING)
   int32_t ring;          // plane staging: next slot to try (k_decode)
   int32_t paired;        // blocks written out interleaved from staged planes (statistics)
-  int32_t pad2[2];
+  int32_t pad2[4];
 };
 
 __device__ __forceinline__ int32_t ld_le32(const uint8_t* p) {

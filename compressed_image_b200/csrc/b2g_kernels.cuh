@@ -16,15 +16,10 @@
 //   k_filter        standalone filters (K1-K4).
 #pragma once
 #include "b2g_lzenc.cuh"
-#include "b2g_seq.cuh"
 #include "b2g_filters.cuh"
 #include "b2g_zstd.cuh"
 
 namespace b2g {
-
-#ifdef B2G_SIM
-inline unsigned long long& sim_two_phase_hits() { static unsigned long long n = 0; return n; }  // test visibility only
-#endif
 
 // ---- decode plan ---------------------------------------------------------------------------------------------------
 struct PlanArgs {
@@ -36,13 +31,12 @@ struct PlanArgs {
   int32_t n;
   int32_t max_block;   // largest blocksize the decode kernels can take (window or scratch slab)
   int32_t zstd_ok;     // the zstd kernel will be launched
-  long long rec_cap;   // sequence records the batch's record buffer can hold (0: no two-phase decode)
 };
 
 __device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_block, int zstd_ok) {
   const uint8_t* src = ch.src;
   const int32_t srcsize = ch.src_bytes;
-  d.nitems = 0; d.nblocks = 0; d.nbytes = 0; d.vts = 0; d.nstreams = 1; d.serial = 0; d.rec_base = -1; d.rec_div = 2;
+  d.nitems = 0; d.nblocks = 0; d.nbytes = 0; d.vts = 0; d.nstreams = 1; d.serial = 0;
   if (srcsize < kHdrMin) return kErrRead;
   d.version = src[0];
   d.flags = src[2];
@@ -53,6 +47,10 @@ __device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_bloc
   if (cbytes < kHdrMin) return kErrHeader;
   if (blocksize <= 0 || (nbytes > 0 && blocksize > nbytes)) return kErrHeader;
   if (blocksize > kMaxBlocksize) return kErrHeader;
+  // a negative size would make this chunk's item count negative and shift every later chunk of the batch (the reference
+  // decodes one chunk per call and fails it further down: blosc2.c:2937 "nbytes > destsize" never fires, the block loop
+  // does not run, and it returns the negative size)
+  if (nbytes < 0) return kErrHeader;
   if (d.typesize == 0) return kErrHeader;
   const int ts = d.typesize;
   const bool ext = (d.flags & kFlagShuffle) && (d.flags & kFlagBitshuffle);
@@ -124,34 +122,18 @@ __device__ __forceinline__ int plan_one(const DChunk& ch, DInfo& d, int max_bloc
 }
 
 constexpr int kPlanThreads = 1024;
-constexpr size_t kPlanSmemBytes = kPlanThreads * (2 * sizeof(int32_t) + sizeof(long long));
+constexpr size_t kPlanSmemBytes = kPlanThreads * 2 * sizeof(int32_t);
 
 __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
   int32_t* cnt = (int32_t*)dyn_smem();  // [2][blockDim.x] partial sums
   const int t = (int)threadIdx.x, nt = (int)blockDim.x;
   const int per = (a.n + nt - 1) / nt;
   const int lo = min(a.n, t * per), hi = min(a.n, lo + per);
-  long long* rcnt = (long long*)(cnt + 2 * nt);  // [blockDim.x] record-region partial sums
   int32_t sum[2] = {0, 0};
-  long long rsum = 0;
   for (int i = lo; i < hi; i++) {
     DInfo d;
     int rc = plan_one(a.chunks[i], d, a.max_block, a.zstd_ok);
     if (rc < 0) d.nitems = 0;
-    // Two-phase decode (b2g_seq.cuh) for lz4 / blosclz chunks whose streams fit the u16 record fields.  Every sequence
-    // takes >= 3 (lz4) / >= 2 (blosclz) compressed bytes, so a stream whose payload starts at chunk offset `pos` owns the
-    // records [pos / div, (pos + csize) / div + 1] of the chunk's region: disjoint for disjoint payloads.
-    long long need = 0;
-    if (d.nitems > 0 && !d.special && !d.memcpyed && !d.serial && (d.fmt == kFmtLz4 || d.fmt == kFmtBlosclz)) {
-      const int full = d.nblocks - (d.leftover > 0 ? 1 : 0);
-      const int big = max(full > 0 ? d.blocksize / d.nstreams : 0, d.leftover);
-      if (big <= kSeqMaxStream) {
-        d.rec_div = d.fmt == kFmtLz4 ? 3 : 2;
-        need = (long long)min(d.cbytes, a.chunks[i].src_bytes) / d.rec_div + 2;
-      }
-    }
-    d.rec_base = need > 0 ? rsum : -1;  // provisional, like item_base
-    rsum += need;
     a.res[i].status = rc;
     a.res[i].out_bytes = rc < 0 ? 0 : d.nbytes;
     const int cls = (d.nitems > 0 && !d.special && !d.memcpyed && d.fmt == kFmtZstd) ? 1 : 0;
@@ -162,7 +144,6 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
   }
   cnt[t] = sum[0];
   cnt[nt + t] = sum[1];
-  rcnt[t] = rsum;
   __syncthreads();
   if (t == 0) {  // serial scan over <= 1024 partials
     for (int k = 0; k < 2; k++) {
@@ -170,18 +151,13 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
       for (int i = 0; i < nt; i++) { int32_t v = cnt[k * nt + i]; cnt[k * nt + i] = run; run += v; }
       a.ctl[k].total_items = run;
       a.ctl[k].ticket = 0;
-      a.ctl[k].parse_ticket = 0;
-      a.ctl[k].replayed = 0;
       a.ctl[k].ring = 0;
       a.ctl[k].paired = 0;
       a.base[k * (a.n + 1) + a.n] = run;
     }
-    long long run = 0;
-    for (int i = 0; i < nt; i++) { long long v = rcnt[i]; rcnt[i] = run; run += v; }
   }
   __syncthreads();
   int32_t off[2] = {cnt[t], cnt[nt + t]};
-  const long long roff = rcnt[t];
   for (int i = lo; i < hi; i++) {
     const int cls = a.info[i].cls;
     const int32_t nit = a.info[i].nitems;
@@ -189,12 +165,6 @@ __global__ void __launch_bounds__(1024) k_plan_decode(PlanArgs a) {
     a.base[(a.n + 1) + i] = off[1];
     a.info[i].item_base = off[cls];
     off[cls] += nit;
-    long long rb = a.info[i].rec_base;
-    if (rb >= 0) {
-      rb += roff;
-      const long long need = (long long)min(a.info[i].cbytes, a.chunks[i].src_bytes) / a.info[i].rec_div + 2;
-      a.info[i].rec_base = rb + need <= a.rec_cap ? rb : -1;  // out of record space: the one-pass decoder takes the chunk
-    }
   }
 }
 
@@ -231,9 +201,6 @@ struct DecodeArgs {
   int32_t wstride;       // bytes of shared memory per warp: wcap (+ the zstd work area)
   uint8_t* slab;         // global scratch window for streams that do not fit in wcap: one per warp of the grid
   int64_t slab_stride;
-  ItemRec* itab;         // [itab_cap] per work item: what k_parse found (class 0 only; nullptr = one-pass decode only)
-  int32_t itab_cap;
-  uint2* rec;            // sequence records (regions: DInfo::rec_base)
   // Plane pairing: the byte planes of a split block are decoded by different warps at different times.  Instead of each
   // scattering its bytes into the raw block (partial sectors, read-modify-write in L2 / HBM), the planes that finish
   // first are parked in an L2-resident ring of staging slots and the LAST plane's warp writes the whole block
@@ -266,70 +233,6 @@ __device__ __forceinline__ DGeom decode_geometry_of(const DInfo& d, int it) {
   g.neblock = g.bsize / g.ns;
   g.scatter = g.ns > 1 && !d.serial;
   return g;
-}
-
-// ---- parse -----------------------------------------------------------------------------------------------------------
-// One LANE per stream item: directory walk, then the token chain of the stream into sequence records (b2g_seq.cuh).
-// Anything unusual (special streams aside) leaves nseq = 0 and the item to the one-pass decoder of k_decode, which owns
-// the accept / reject decision and the error codes.
-constexpr int kParseThreads = 32;   // one warp = 32 streams = 32 pieces of shared memory
-constexpr size_t kParseSmemBytes = (kParseThreads / 32) * 32 * kPieceBytes + 16;  // pc_word may read one word past a piece
-
-__global__ void __launch_bounds__(kParseThreads) k_parse(DecodeArgs a) {
-  const int lane = lane_id();
-  uint8_t* sm = dyn_smem() + (size_t)warp_id() * 32 * kPieceBytes;
-  for (;;) {
-    int first = 0;
-    if (lane == 0) first = atomicAdd(&a.ctl->parse_ticket, 32);
-    first = __shfl_sync(kFull, first, 0);
-    const int total = min(a.ctl->total_items, a.itab_cap);
-    if (first >= total) break;
-    const int item = first + lane;
-    ItemRec ir;
-    ir.pos = 0; ir.csize = 0; ir.nseq = 0; ir.slack = 0;
-    LaneParse L;
-    L.in = nullptr; L.rec = nullptr; L.n = 0; L.cap = 0; L.maxrec = 0; L.slack = 0;
-    bool active = false, lz4 = true;
-    if (item < total) {
-      const int c = find_chunk(a.base, a.n, item, 0);
-      const DInfo& d = a.info[c];
-      const long long rec_base = d.rec_base;
-      if (rec_base >= 0) {
-        const DGeom g = decode_geometry_of(d, item - d.item_base);
-        const uint8_t* src = a.chunks[c].src;
-        const int32_t srcsize = min(a.chunks[c].src_bytes, d.cbytes);
-        const int32_t need = decode_window_bytes(g.neblock, d.fmt);
-        int32_t pos = ld_le32(src + d.hdr + 4 * g.j);
-        bool ok = need <= a.wcap && g.neblock > 0 && pos > 0 && pos < srcsize;
-        int32_t cs = 0;
-        for (int k = 0; ok && k <= g.s; k++) {  // the same walk and checks as decode_streams
-          if (srcsize - pos < 4) { ok = false; break; }
-          cs = ld_le32(src + pos);
-          pos += 4;
-          if (cs > 0 && srcsize - pos < cs) ok = false;
-          if (cs < 0 && srcsize - pos < 1) ok = false;
-          if (ok && k < g.s) pos += cs > 0 ? cs : (cs < 0 ? 1 : 0);
-        }
-        if (ok && cs > 0 && cs < g.neblock) {
-          const int div = d.rec_div;
-          L.in = src + pos; L.n = cs; L.cap = g.neblock;
-          L.rec = a.rec + rec_base + pos / div;
-          L.maxrec = cs / div + 1;
-          lz4 = d.fmt == kFmtLz4;
-          ir.pos = pos; ir.csize = cs;
-          active = true;
-        }
-      }
-    }
-    // lz4 and blosclz streams of one batch are parsed in turn (a batch is nearly always one codec)
-    const unsigned is_lz4 = __ballot_sync(kFull, active && lz4), is_blz = __ballot_sync(kFull, active && !lz4);
-    int nseq = 0;
-    if (is_lz4) { const int r = seq_parse_warp(L, active && lz4, true, sm); if (active && lz4) nseq = r; }
-    if (is_blz) { const int slack = L.slack; const int r = seq_parse_warp(L, active && !lz4, false, sm);
-                  if (active && !lz4) nseq = r; else L.slack = slack; }
-    ir.nseq = nseq; ir.slack = L.slack;
-    if (item < total) a.itab[item] = ir;
-  }
 }
 
 // dst[0..n) = src[0..n) with dst in shared memory and dst = src (mod 16): the aligned body goes through asynchronous
@@ -636,35 +539,7 @@ __global__ void __launch_bounds__(512, 1) k_decode(DecodeArgs a) {
     jb.s = g.s; jb.s_end = g.s_end; jb.ns = g.ns; jb.neblock = neblock; jb.bsize = bsize; jb.scatter = g.scatter;
     jb.fmt = d.fmt; jb.filter = d.filter; jb.typesize = d.typesize; jb.version = d.version; jb.item = item;
     int err;
-    bool done = false;
-    if (!Z && a.itab != nullptr && item < a.itab_cap && d.rec_base >= 0) {
-      // two-phase decode: k_parse left the stream's sequence records; replay them into the window
-      const ItemRec ir = a.itab[item];
-      if (ir.nseq > 0) {
-        const uint8_t* payload = ch.src + ir.pos;
-        const int m = (int)((uintptr_t)payload & 15);
-        const int room = a.wcap - ir.csize - m;
-        const int ao = (room & ~15) + m;  // ao + csize <= wcap, (win + ao) = payload (mod 16)
-        if (room >= 0 && ir.slack <= ao && need <= a.wcap) {
-          stage_payload(win_s + ao, payload, ir.csize, lane);
-          __syncwarp();
-          const int got = seq_execute_warp(a.rec + d.rec_base + ir.pos / d.rec_div, ir.nseq, win_s, ao, ir.csize,
-                                           neblock, (uint4*)(win_s + a.wcap));
-          __syncwarp();
-          if (got == neblock) {
-            unfilter_streams(a, jb, win_s);
-#ifdef B2G_SIM
-            if (lane == 0) sim_two_phase_hits()++;
-#endif
-            if (lane == 0) atomicAdd(&a.ctl->replayed, 1);
-            done = true;
-            err = 0;
-          }
-        }
-      }
-    }
-    if (done) {}
-    else if (need <= a.wcap) err = decode_streams<Z, true, true>(a, jb, win_s, a.wcap, zw);
+    if (need <= a.wcap) err = decode_streams<Z, true, true>(a, jb, win_s, a.wcap, zw);
     else if (direct) err = decode_streams<Z, false, false>(a, jb, raw, bsize, zw);
     else err = decode_streams<Z, true, false>(a, jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw);
     if (err && lane == 0) set_status(a.res, c, err);

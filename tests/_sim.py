@@ -19,13 +19,12 @@ def lib():
     if _lib is None:
         subprocess.run(["make", "-s", "-C", SIM_DIR], check=True, capture_output=True)
         L = C.CDLL(os.path.join(SIM_DIR, "libb2gsim.so"))
-        L.sim_decompress_batch.argtypes = [ci, pvp, pi32, pvp, pi32, pi32, pi32, ci, ci, ci, ci, ci, ci]
+        L.sim_decompress_batch.argtypes = [ci, pvp, pi32, pvp, pi32, pi32, pi32, ci, ci, ci, ci, ci]
         L.sim_compress_batch.argtypes = [ci, ci, ci, ci, ci, ci, pvp, pi32, pvp, pi32, pi32, pi32, ci, ci, ci]
         L.sim_filter.argtypes = [ci, ci, ci, ci, vp, vp, i64, ci, ci]
         L.sim_stream_decode.argtypes = [ci, vp, ci, vp, ci]
         L.sim_stream_encode.argtypes = [ci, vp, ci, vp, ci, ci]
         L.sim_collectives.restype = C.c_ulonglong
-        L.sim_two_phase_hits.restype = C.c_ulonglong
         L.sim_last_paired.restype = C.c_int
         _lib = L
     return _lib
@@ -36,7 +35,7 @@ def _ptrs(arrs):
 
 
 def decompress_batch(chunks, caps=None, win_bytes=33280, max_block=None, grid=2, zstd_ok=True, srcsizes=None,
-                     two_phase=1, pair=1):
+                     pair=1):
     """-> list of (status, bytes)."""
     n = len(chunks)
     chunks = [np.ascontiguousarray(c) for c in chunks]
@@ -54,7 +53,7 @@ def decompress_batch(chunks, caps=None, win_bytes=33280, max_block=None, grid=2,
     out = (C.c_int32 * n)()
     st = (C.c_int32 * n)()
     rc = lib().sim_decompress_batch(n, _ptrs(chunks), (C.c_int32 * n)(*srcsizes), _ptrs(outs), (C.c_int32 * n)(*caps),
-                                    out, st, win_bytes, max_block, grid, 1 if zstd_ok else 0, two_phase, pair)
+                                    out, st, win_bytes, max_block, grid, 1 if zstd_ok else 0, pair)
     assert rc == 0 or any(s < 0 for s in st), "a plane staging slot was leaked"
 
     res = []

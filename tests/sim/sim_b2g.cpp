@@ -18,7 +18,7 @@ extern "C" {
 // that need more use the slab path).  out[i] = nbytes or 0, status[i] = 0 or error.
 int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes, void* const* dsts,
                          const int32_t* caps, int32_t* out, int32_t* status, int win_bytes, int max_block, int grid,
-                         int zstd_ok, int two_phase, int pair) {
+                         int zstd_ok, int pair) {
   std::vector<DChunk> ch(n);
   std::vector<DInfo> info(n);
   std::vector<DResult> res(n);
@@ -35,24 +35,13 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   PlanArgs pa;
   pa.chunks = ch.data(); pa.info = info.data(); pa.res = res.data(); pa.base = base.data(); pa.ctl = ctl;
   pa.n = n; pa.max_block = max_block; pa.zstd_ok = zstd_ok;
-  long long rec_cap = 0, itab_cap = 0;
-  for (int i = 0; i < n; i++) {
-    rec_cap += std::min<long long>(std::max(srcsizes[i], 0), (long long)std::max(caps[i], 0) + 32) / 2 + 2;
-    itab_cap += ((long long)std::max(caps[i], 0) / 64 + 2) * kMaxStreams;
-  }
-  if (two_phase == 0) rec_cap = itab_cap = 0;
-  if (two_phase == 2) rec_cap = rec_cap / 6;  // not every chunk gets a record region
-  std::vector<uint2> recs(rec_cap + 2);
-  std::vector<ItemRec> itab(itab_cap + 1);
-  pa.rec_cap = rec_cap;
   cusim::launch(dim3(1), dim3(kPlanThreads), kPlanSmemBytes, [&] { k_plan_decode(pa); });
   const int warps = 2;  // independent workers per simulated CTA
   const size_t stride = au((size_t)decode_window_bytes(max_block, kFmtBlosclz) + 256, 256);
   std::vector<uint8_t> slab(stride * grid * warps + 256);
   DecodeArgs da;
   da.chunks = ch.data(); da.info = info.data(); da.res = res.data(); da.base = base.data(); da.ctl = &ctl[0];
-  da.n = n; da.wcap = win_bytes; da.wstride = win_bytes + kSeqGroupSmem; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
-  da.itab = itab_cap > 0 ? itab.data() : nullptr; da.itab_cap = (int32_t)itab_cap; da.rec = recs.data();
+  da.n = n; da.wcap = win_bytes; da.wstride = win_bytes; da.slab = slab.data(); da.slab_stride = (int64_t)stride;
   // plane pairing: few slots on purpose (the no-free-slot path must run too); pair == 0 switches it off
   long long pair_cap = 0;
   for (int i = 0; i < n; i++) pair_cap += ((long long)std::max(caps[i], 0) / 64 + 2) * kMaxStreams;
@@ -62,7 +51,6 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   da.stage = pair ? stage.data() : nullptr;
   da.slotflag = pairmeta.data(); da.mail = da.slotflag + nslots; da.blkcnt = da.mail + 2 * pair_cap;
   da.nslots = nslots; da.slot_bytes = win_bytes; da.pair_cap = (int32_t)pair_cap;
-  if (itab_cap > 0) cusim::launch(dim3(grid), dim3(kParseThreads), kParseSmemBytes, [&] { k_parse(da); });
   cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<false>(da); });
   if (zstd_ok) {
     da.base = base.data() + (n + 1);
@@ -175,7 +163,6 @@ int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int
 }
 
 unsigned long long sim_collectives() { return cusim::S().collectives; }
-unsigned long long sim_two_phase_hits() { return b2g::sim_two_phase_hits(); }
 int sim_last_paired() { return g_last_paired; }
 
 }  // extern "C"

@@ -272,29 +272,24 @@ def test_async_host_batches_on_two_contexts():
         cd.wait()   # nothing in flight: a no-op
 
 
-def test_two_phase_decode_opt_in(monkeypatch):
-    """B2G_TWO_PHASE=1 (read when a context is created): k_parse + record replay decode the lz4 / blosclz reference
-    chunks bit-exactly, and damaged payloads get the one-pass decoder's decisions."""
-    from compressed_image_b200 import _b2g
+def test_damaged_payloads_same_decisions_as_reference():
+    """Byte flips in lz4 / blosclz payloads: the GPU decoder accepts / rejects what the reference library does, and
+    equals it byte for byte where the damaged chunk still decodes (device-resident and host-pointer paths)."""
     g = _gpu()
-    monkeypatch.setenv("B2G_TWO_PHASE", "1")
     keys = [k for k in _golden.REF_KEYS if "_c%d_" % _data.LZ4 in k or "_c%d_" % _data.BLOSCLZ in k]
-    chunks = [_golden.ref_chunk(k) for k in keys]
-    with _b2g.Context(_data.LZ4, 9, 1, _data.SHUFFLE, 32768) as cx:
-        for device in (False, True):
-            res = g.decompress_batch(chunks, context=cx, device=device)
-            for k, (st, out) in zip(keys, res):
-                assert st == 0 and np.array_equal(out, _data.make_case(_golden.MANIFEST["ref_chunks"][k]["case"])), k
-        rng = np.random.default_rng(11)
-        key = [k for k in keys if k.startswith("text_n300000")][0]
+    rng = np.random.default_rng(11)
+    bad = []
+    for key in [k for k in keys if k.startswith("text_n300000")]:
         chunk = _golden.ref_chunk(key)
-        bad = []
         for _ in range(24):
             b = chunk.copy()
-            b[int(rng.integers(32, chunk.size))] ^= np.uint8(rng.integers(1, 256))
+            for _ in range(int(rng.integers(1, 4))):
+                b[int(rng.integers(32, chunk.size))] ^= np.uint8(rng.integers(1, 256))
             bad.append(b)
-        res = g.decompress_batch(bad, caps=[300000] * len(bad), context=cx)
-    monkeypatch.delenv("B2G_TWO_PHASE")
-    ref = g.decompress_batch(bad, caps=[300000] * len(bad))
-    for (st, out), (st0, out0) in zip(res, ref):
-        assert st == st0 and np.array_equal(out, out0)
+    for device in (False, True):
+        res = g.decompress_batch(bad, caps=[300000] * len(bad), device=device)
+        for b, (st, out) in zip(bad, res):
+            rc, exp = _libs.ref_decompress(b, cap=300000) if _libs.ref() else _libs.oracle_decompress(b, cap=300000)
+            assert (st < 0) == (rc < 0), (st, rc)
+            if rc >= 0:
+                assert np.array_equal(out, exp)

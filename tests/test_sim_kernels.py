@@ -231,30 +231,11 @@ def test_lz4_offset_zero_stream(ml):
     assert r == cap and np.array_equal(out, exp)
 
 
-# ---- two-phase decode (k_parse -> sequence records -> replay) ---------------------------------------------------------
-def test_two_phase_is_taken_and_equals_one_pass():
-    """lz4 / blosclz reference chunks go through the record path (counted), and decode identically with it switched off
-    or short of record space."""
-    keys = [k for k in _golden.REF_KEYS if "_c%d_" % _data.LZ4 in k or "_c%d_" % _data.BLOSCLZ in k]
-    chunks = [_golden.ref_chunk(k) for k in keys]
-    h0 = _sim.lib().sim_two_phase_hits()
-    res1 = _sim.decompress_batch(chunks, grid=3, two_phase=1)
-    h1 = _sim.lib().sim_two_phase_hits()
-    res0 = _sim.decompress_batch(chunks, grid=3, two_phase=0)
-    h2 = _sim.lib().sim_two_phase_hits()
-    res2 = _sim.decompress_batch(chunks, grid=3, two_phase=2)
-    h3 = _sim.lib().sim_two_phase_hits()
-    assert h1 - h0 > 100 and h2 == h1 and 0 < h3 - h2 < h1 - h0
-    for k, a, b, c in zip(keys, res1, res0, res2):
-        exp = _data.make_case(_golden.MANIFEST["ref_chunks"][k]["case"])
-        assert a[0] == 0 and b[0] == 0 and c[0] == 0, k
-        assert np.array_equal(a[1], exp) and np.array_equal(b[1], exp) and np.array_equal(c[1], exp), k
-
-
+# ---- batched sequence decode (parse ahead, lane-per-sequence copies) ---------------------------------------------------
 @pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
-def test_two_phase_same_decisions_on_damaged_payloads(codec):
-    """Byte flips all over the payload: the record path and the one-pass decoder agree with the oracle on accept /
-    reject, and on every byte when the damaged chunk still decodes."""
+def test_same_decisions_on_damaged_payloads(codec):
+    """Byte flips all over the payload: the decoder agrees with the oracle on accept / reject whatever the window slack
+    (= how many sequences a batch may hold), and on every byte when the damaged chunk still decodes."""
     rng = np.random.default_rng(7 + codec)
     key = [k for k in _golden.REF_KEYS if k.startswith("text_n300000") and "_c%d_" % codec in k][0]
     chunk = _golden.ref_chunk(key)
@@ -265,8 +246,8 @@ def test_two_phase_same_decisions_on_damaged_payloads(codec):
         for _ in range(int(rng.integers(1, 4))):
             b[int(rng.integers(32, chunk.size))] ^= np.uint8(rng.integers(1, 256))
         bad.append(b)
-    r1 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad), two_phase=1)
-    r0 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad), two_phase=0)
+    r1 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad))
+    r0 = _sim.decompress_batch(bad, caps=[nbytes] * len(bad), win_bytes=32768 + 1040 + 96)
     for i in range(len(bad)):
         rc, exp = _libs.oracle_decompress(bad[i], cap=nbytes)
         assert (r1[i][0] < 0) == (rc < 0) and (r0[i][0] < 0) == (rc < 0), (i, r1[i][0], r0[i][0], rc)
@@ -275,17 +256,15 @@ def test_two_phase_same_decisions_on_damaged_payloads(codec):
             assert np.array_equal(r1[i][1], exp) and np.array_equal(r0[i][1], exp)
 
 
-def test_two_phase_gpu_compressed_chunks():
-    """Chunks from the simulated GPU encoder (long runs, overlapping matches, tiny tails) through the record path."""
+def test_gpu_compressed_chunks_decode():
+    """Chunks from the simulated GPU encoder (long runs, overlapping matches, tiny tails)."""
     srcs = [_data.make_data(k, n, ts, seed=n) for k in ("iota", "sparse", "text", "f32", "zeros")
             for n, ts in ((70001, 1), (131072, 2), (65536 + 24, 4))]
     for codec, filt in ((_data.LZ4, _data.SHUFFLE), (_data.BLOSCLZ, _data.BITSHUFFLE), (_data.BLOSCLZ, _data.SHUFFLE)):
         for ts in (1, 2, 4):
             mine = [s for s in srcs if s.size % ts == 0][:6]
             enc = _sim.compress_batch(mine, codec, 9, ts, filt, 32768)
-            h0 = _sim.lib().sim_two_phase_hits()
-            dec = _sim.decompress_batch([c for _, c in enc], two_phase=1, win_bytes=34816)
-            assert _sim.lib().sim_two_phase_hits() > h0, (codec, filt, ts)
+            dec = _sim.decompress_batch([c for _, c in enc], win_bytes=34816)
             for s, (st, out) in zip(mine, dec):
                 assert st == 0 and np.array_equal(out, s.view(np.uint8).reshape(-1))
 
@@ -303,15 +282,14 @@ def _noisy_with_repeats(n, gap, mlen, seed):
 
 @pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
 @pytest.mark.parametrize("gap,mlen", [(40, 12), (70, 8), (200, 24), (33, 5), (1000, 40)])
-def test_two_phase_long_literal_runs_in_place(codec, gap, mlen):
+def test_long_literal_runs_in_place(codec, gap, mlen):
     srcs = [_noisy_with_repeats(65536, gap, mlen, seed) for seed in (1, 2)]
     for ts, bs in ((1, 16384), (2, 32768), (1, 32768)):
         enc = _sim.compress_batch(srcs, codec, 9, ts, _data.SHUFFLE, bs)
         chunks = [c for _, c in enc]
         exp = [_libs.oracle_decompress(c)[1] for c in chunks]
-        for wb in (17040, 34000):
-            h0 = _sim.lib().sim_two_phase_hits()
-            dec = _sim.decompress_batch(chunks, two_phase=1, win_bytes=wb)
+        for wb in (16384 + 96, 17040, 18000, 34000):
+            dec = _sim.decompress_batch(chunks, win_bytes=wb)
             for s, e, (st, out) in zip(srcs, exp, dec):
                 assert st == 0 and np.array_equal(out, s) and np.array_equal(e, s), (ts, bs, wb)
 
@@ -332,14 +310,13 @@ def test_plane_pairing_matches_plain_scatter(ts, codec):
         chunks = [c for _, c in _sim.compress_batch(srcs, codec, 9, ts, _data.SHUFFLE, 32768)]
     got = {}
     for pair in (1, 2, 0):
-        for tp in (0, 1):
-            res = _sim.decompress_batch(chunks, grid=3, two_phase=tp, pair=pair)
-            paired = _sim.lib().sim_last_paired()
-            for s, (st, out) in zip(srcs, res):
-                assert st == 0 and np.array_equal(out, s.view(np.uint8).reshape(-1)), (pair, tp)
-            got[(pair, tp)] = paired
-    assert got[(1, 0)] >= 8 and got[(1, 1)] >= 8
-    assert got[(0, 0)] == 0 and got[(0, 1)] == 0
+        res = _sim.decompress_batch(chunks, grid=3, pair=pair)
+        paired = _sim.lib().sim_last_paired()
+        for s, (st, out) in zip(srcs, res):
+            assert st == 0 and np.array_equal(out, s.view(np.uint8).reshape(-1)), pair
+        got[pair] = paired
+    assert got[1] >= 8
+    assert got[0] == 0
 
 
 def test_plane_pairing_unaligned_destination_falls_back():
