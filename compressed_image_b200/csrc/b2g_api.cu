@@ -194,18 +194,33 @@ struct DecGeom {
   int wcap, wstride, warps, grid;
   size_t smem;
 };
+// lz4 / blosclz streams are decoded in place in batches of up to 32 sequences, and a batch may only produce as many bytes
+// as lie between its output and its own (staged) input.  A stream that barely compresses runs with that distance down at
+// the window's slack, so the windows get kDecodeSlack bytes more than decoding needs; whatever shared memory the warp
+// count then leaves over is handed out as well (16 KiB lz4 streams: 13 windows of 17872 bytes per SM).
+constexpr int kDecodeSlack = 1024, kDecodeSlackMax = 4096;
 int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g, bool any_blosclz = true) {
   if (stream_bytes > 96 * 1024) stream_bytes = 16 * 1024;  // such streams decode through the global slab anyway
-  g.wcap = std::max(decode_window_bytes(std::max(stream_bytes, 1), any_blosclz ? kFmtBlosclz : kFmtLz4), 1024);
-  g.wstride = g.wcap + (zstd ? (int)align_up(sizeof(ZWork), 16) : 0);
-  int best = 0;
+  static const int slack = [] { const char* e = getenv("B2G_DECODE_SLACK"); return e ? std::max(atoi(e), 0) : kDecodeSlack; }();
+  const int need = std::max(decode_window_bytes(std::max(stream_bytes, 1), any_blosclz ? kFmtBlosclz : kFmtLz4), 1024);
+  const int extra = zstd ? (int)align_up(sizeof(ZWork), 16) : 0;
+  g.wcap = need + (zstd ? 0 : slack);
+  g.wstride = g.wcap + extra;
+  if ((size_t)g.wstride > 227 * 1024) { g.wcap = need; g.wstride = need + extra; }
+  int best = 0, ctas = 1;
   g.warps = 1;
   for (int w = 1; w <= 16; w++) {
     const size_t cta = (size_t)w * g.wstride;
     if (cta > 227 * 1024) break;
     int n = (int)((228 * 1024) / (cta + 1024));
     n = std::min(n, std::min(32, 64 / w));
-    if (w * n >= best) { best = w * n; g.warps = w; }
+    if (w * n >= best) { best = w * n; g.warps = w; ctas = n; }
+  }
+  if (!zstd) {  // the same warps, the largest windows
+    const size_t per_cta = std::min<size_t>((228 * 1024) / ctas - 1024, 227 * 1024);
+    const int room = (int)(per_cta / g.warps) & ~15;
+    g.wcap = std::max(g.wcap, std::min(room, need + std::max(slack, kDecodeSlackMax)));
+    g.wstride = g.wcap;
   }
   g.smem = (size_t)g.warps * g.wstride;
   const void* fn = zstd ? (const void*)k_decode<true> : (const void*)k_decode<false>;

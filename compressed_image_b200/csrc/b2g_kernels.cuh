@@ -286,13 +286,13 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
         if (SMEM) stage_payload(win + a, payload, csize, lane);  // asynchronous 16-byte copies, all in flight at once
         else copy_bytes(win + a, payload, csize, lane, 32);
         __syncwarp();
-        got = fmt == kFmtLz4 ? lz4_decode_warp_t<true>(win + a, csize, win, neblock, a)
+        got = fmt == kFmtLz4 ? lz4_decode_warp_t<true, SMEM>(win + a, csize, win, neblock, a)
                              : blosclz_decode_warp_t<true>(win + a, csize, win, neblock, a);
       }
     }
     if (got == -2) {  // not staged, or the output caught up with the staged input: decode from the chunk itself
       __syncwarp();
-      got = fmt == kFmtLz4 ? lz4_decode_warp(payload, csize, win, neblock)
+      got = fmt == kFmtLz4 ? lz4_decode_warp_t<false, SMEM>(payload, csize, win, neblock, 0)
                            : blosclz_decode_warp(payload, csize, win, neblock);
     }
   }

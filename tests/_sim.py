@@ -30,6 +30,13 @@ def lib():
     return _lib
 
 
+def decode_stats(reset=True):
+    """-> dict of the batched-decode counters since the last reset."""
+    out = (C.c_ulonglong * 5)()
+    lib().sim_decode_stats(out, 1 if reset else 0)
+    return dict(zip(("batches", "batch_seqs", "lane_matches", "ordered_matches", "general_seqs"), [int(v) for v in out]))
+
+
 def _ptrs(arrs):
     return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
 

@@ -164,5 +164,12 @@ int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int
 
 unsigned long long sim_collectives() { return cusim::S().collectives; }
 int sim_last_paired() { return g_last_paired; }
+// lz4 / blosclz batched decode counters: [batches, sequences executed in batches, (unused), matches copied in stream
+// order by the whole warp, sequences taken by the general path]
+void sim_decode_stats(unsigned long long* out5, int reset) {
+  SimDecodeStats& s = sim_decode_stats();
+  out5[0] = s.batches; out5[1] = s.batch_seqs; out5[2] = s.lane_matches; out5[3] = s.ordered_matches; out5[4] = s.general_seqs;
+  if (reset) s = SimDecodeStats{0, 0, 0, 0, 0};
+}
 
 }  // extern "C"
