@@ -209,7 +209,7 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, F&& fn) {
       for (int w = 0; w < nwarps; w++) {
         // keep running this warp's lanes while any of them can make progress without the rest of the CTA
         for (;;) {
-          bool ran_nonspin = false;
+          bool ran_nonspin = false, spun = false;
           int lo = w * 32, hi = std::min(nthreads, lo + 32);
           for (int t = lo; t < hi; t++) {
             Fiber& f = fibers[(size_t)c * nthreads + t];
@@ -220,8 +220,11 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, F&& fn) {
             progress = true;
             if (f.done) alive--;
             else if (!f.spin) ran_nonspin = true;
+            else spun = true;
           }
-          if (!ran_nonspin) break;
+          // a lane that polls is waiting for another warp: give the rest of the grid a turn (a polling loop may hold
+          // warp collectives, so "only spinning lanes ran" alone would never become true)
+          if (!ran_nonspin || spun) break;
         }
       }
     }

@@ -1,8 +1,9 @@
-# quick GPU check: parity tests, a short bench (kernel numbers only), launch list, and one ncu --set full capture of k_decode
+# quick GPU check: parity tests, a short bench (kernel numbers only); optional ncu --set full capture
+#   usage: bash tools/gpu_quick.sh [ncu <kernel-regex> <launch-skip> <out-name>]
 set -x
 (timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -15) > gpurun_out/q_pytest.log 2>&1
+tail -3 gpurun_out/q_pytest.log
 (timeout 600 python bench.py --steps 10 --warmup 3 --kernels-only) > gpurun_out/q_bench.log 2>&1
-cat gpurun_out/q_pytest.log | tail -5
 python - <<'PY'
 import json
 for f in ('gpurun_out/q_bench.log',):
