@@ -4,7 +4,11 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <climits>
+#include <condition_variable>
+#include <functional>
+#include <thread>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -75,21 +79,46 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // One pipeline lane: a stream plus every per-batch work buffer, so that sub-batches of a host-pointer call can be in
 // flight on different lanes at once (H2D of one overlapping the kernels of another and the D2H of a third).  The
 // device-resident entry points use lane 0 on the caller's stream.
-constexpr int kLanes = 6;  // lanes a context owns; host-pointer batches rotate over the first g_lanes of them
-static const int g_lanes = [] { const char* e = getenv("B2G_LANES"); int v = e ? atoi(e) : 6; return v < 1 ? 1 : (v > kLanes ? kLanes : v); }();
+constexpr int kLanes = 16; // lanes a context owns; host-pointer batches rotate over the first g_lanes of them, the
+                           // staged path gives worker thread t the lanes t and t + g_lanes
+constexpr int kStagePieces = 8;
+static const int g_lanes = [] { const char* e = getenv("B2G_LANES"); int v = e ? atoi(e) : 6; return v < 1 ? 1 : (v > kLanes / 2 ? kLanes / 2 : v); }();
 struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
   DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_stage, d_pair;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
+  HostBuf h_in, h_out;                               // pinned bounce buffers of the staged (pageable-caller) path
+  cudaEvent_t piece[kStagePieces] = {};              // D2H pieces of a staged sub-batch landed in h_out
+  size_t st_out_lo = 0, st_piece = 0;                // staged sub-batch between its issue and its drain
+  int st_npieces = 0, st_per = 1;
+  std::vector<size_t> st_loc;
   void release() {
     for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_stage, &d_pair}) b->release();
-    for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base}) b->release();
+    for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base, &h_in, &h_out}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
+    for (auto& e : piece) if (e) cudaEventDestroy(e);
     if (res_ready) cudaEventDestroy(res_ready);
     if (stream) cudaStreamDestroy(stream);
   }
+};
+
+// Worker threads of a context, one per lane, for host-pointer batches whose buffers are PAGEABLE (what
+// compressed::channel<T> hands over: std::span over a std::vector, wrapper.h:167-185, 236-259).  cudaMemcpyAsync on
+// pageable memory is a synchronous bounce inside the driver at a fraction of the link speed; instead thread t takes the
+// sub-batches t, t + T, ... of the batch and runs each one through its lane: memcpy of the inputs into the lane's pinned
+// buffer (pipelined with the H2D copies of the pieces already there), kernels, D2H into the lane's pinned buffer,
+// memcpy out to the caller's buffers.  T memcpy threads keep the host memory system as busy as the link.
+struct HostPool {
+  std::vector<std::thread> th;
+  std::mutex m;
+  std::condition_variable go, done;
+  uint64_t gen = 0;
+  int nsub = 0, running = 0, rc = 0;
+  bool quit = false;
+  std::function<int(int, int)> issue, drain;   // (sub-batch, lane) -> rc: everything up to the enqueued D2H copies /
+                                               // the rest (wait, memcpy out to the caller)
 };
 
 struct b2g_ctx {
@@ -97,12 +126,11 @@ struct b2g_ctx {
   int dev = 0, sms = 0;
   Lane lanes[kLanes];
   float last_ms[2] = {0, 0};
-  int64_t launches = 0;
+  std::atomic<int64_t> launches{0};
   // geometry
   int blocksize = 32768;   // context blocksize (compress) / largest block the decode path is sized for (slab, plan)
   int stream_hint = 32768; // stream size the decode windows are sized for on the device-resident path
   int win_bytes = 32768;   // shared-memory window (standalone filters)
-  int max_grid_warps = 0;  // most worker warps any launch of this context has used (sizes the slab)
   bool geometry_ready = false;
   bool pair_planes = true; // B2G_PAIR_PLANES=0 at creation: every plane scatters its own bytes
   // device + pinned work buffers
@@ -111,7 +139,9 @@ struct b2g_ctx {
   b2g_chunk* pend = nullptr;
   int pend_n = 0;
   cudaStream_t pend_stream = nullptr;
-  int pend_kind = 0;                 // 0 device-resident, 1 host decompress, 2 host compress
+  int pend_kind = 0;                 // 0 device-resident, 1 host decompress, 2 host compress, 3 staged (worker threads)
+  HostPool* pool = nullptr;
+  std::vector<size_t> st_in_off, st_out_off, st_in_len, st_out_len;   // staged batch: per chunk (caller's numbering)
   std::vector<int> pend_bounds;      // sub-batch boundaries of the host-pointer batch in flight
   std::vector<size_t> pend_out_off;  // compress: where each chunk sits in d_out
   std::vector<int> pend_order;       // batch position -> index into the caller's array (batches are processed in host
@@ -244,8 +274,9 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   gz = g;
   if (want_zstd) if (int rc = decode_geometry(c, stream_bytes, true, gz)) return rc;
   // slab: windows for streams larger than the shared-memory window, one per warp of the grid
-  c->max_grid_warps = std::max(c->max_grid_warps, std::max(g.grid * g.warps, gz.grid * gz.warps));
-  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)c->max_grid_warps)) return rc;
+  // (sized for THIS launch: a running maximum over earlier geometries would multiply a later large-block stride by a
+  // warp count that belonged to small blocks)
+  if (int rc = L.d_slab.ensure(slab_stride(c) * (size_t)std::max(g.grid * g.warps, gz.grid * gz.warps))) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = L.d_info.ensure(sizeof(DInfo) * (size_t)n)) return rc;
   if (int rc = L.d_res.ensure(sizeof(DResult) * (size_t)n)) return rc;
@@ -552,6 +583,9 @@ int interleave_device(b2g_ctx* c, bool to_interleaved, int typesize, int nch, vo
 
 extern "C" {
 
+static int pool_wait(b2g_ctx* c);
+static void pool_destroy(b2g_ctx* c);
+
 b2g_ctx* b2g_create(const b2g_params* params) {
   if (!params) { g_last_error = "b2g_create: params == NULL"; return nullptr; }
   int ndev = 0;
@@ -584,6 +618,7 @@ b2g_ctx* b2g_create(const b2g_params* params) {
 void b2g_destroy(b2g_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->dev);
+  if (c->pool) { if (c->pend && c->pend_kind == 3) pool_wait(c); pool_destroy(c); }
   for (Lane& L : c->lanes) if (L.stream) cudaStreamSynchronize(L.stream);
   for (Lane& L : c->lanes) L.release();
   c->d_in.release();
@@ -676,12 +711,18 @@ int b2g_chunk_sizes(const void* chunk, int32_t* nbytes, int32_t* cbytes, int32_t
 // Host-pointer calls are pipelined: the batch is cut into sub-batches of about B2G_SUBBATCH_MB (default 32) MiB of
 // payload which rotate over the context's lanes, so the H2D copies of one sub-batch overlap the kernels of the previous
 // one and the D2H copies of the one before (PCIe is full duplex; the copy engines and the SMs run concurrently).
-static std::vector<int> split_batch(const std::vector<size_t>& payload) {
-  static const size_t target = [] {
+static std::vector<int> split_batch(const std::vector<size_t>& payload, bool staged = false) {
+  static const size_t target_pinned = [] {
     const char* e = getenv("B2G_SUBBATCH_MB");
     long mb = e ? atol(e) : 32;
     return (size_t)std::max(mb, 1L) << 20;
   }();
+  static const size_t target_staged = [] {   // worker threads copy through pinned buffers: smaller pieces pipeline better
+    const char* e = getenv("B2G_STAGED_SUBBATCH_MB");
+    long mb = e ? atol(e) : 12;
+    return (size_t)std::max(mb, 1L) << 20;
+  }();
+  const size_t target = staged ? target_staged : target_pinned;
   std::vector<int> bounds{0};
   size_t acc = 0;
   for (int i = 0; i < (int)payload.size(); i++) {
@@ -707,6 +748,121 @@ static int ensure_sub_events(b2g_ctx* c, int nsub) {
   return 0;
 }
 
+
+// ---- staged host-pointer batches (pageable caller memory) --------------------------------------------------------------
+static bool is_pinned(const void* p) {
+  if (!p) return true;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+// Does any buffer of the batch live in pageable memory?  (B2G_STAGED=1 / 0 forces the answer.)
+static bool batch_needs_staging(const b2g_chunk* chunks, int n) {
+  static const int forced = [] { const char* e = getenv("B2G_STAGED"); return e ? atoi(e) : -1; }();
+  if (forced >= 0) return forced != 0;
+  for (int i = 0; i < n; i++) {
+    if (chunks[i].src_bytes > 0 && !is_pinned(chunks[i].src)) return true;
+    if (chunks[i].dst_capacity > 0 && !is_pinned(chunks[i].dst)) return true;
+  }
+  return false;
+}
+
+static void pool_thread(b2g_ctx* c, int t, int nthreads) {
+  cudaSetDevice(c->dev);
+  HostPool& P = *c->pool;
+  uint64_t seen = 0;
+  for (;;) {
+    std::function<int(int, int)> issue, drain;
+    int nsub = 0;
+    {
+      std::unique_lock<std::mutex> lk(P.m);
+      P.go.wait(lk, [&] { return P.quit || P.gen != seen; });
+      if (P.quit) return;
+      seen = P.gen;
+      issue = P.issue;
+      drain = P.drain;
+      nsub = P.nsub;
+    }
+    // two lanes per thread: sub-batch k + T is on its way (upload, kernels, D2H) while sub-batch k is copied out
+    int rc = 0, prev = -1, prev_lane = 0;
+    for (int k = t; k < nsub; k += nthreads) {
+      const int lane = t + ((k / nthreads) & 1) * nthreads;
+      int r = issue(k, lane);
+      if (prev >= 0) { const int r2 = drain(prev, prev_lane); if (r2 && !rc) rc = r2; }
+      if (r) { if (!rc) rc = r; prev = -1; cudaStreamSynchronize(c->lanes[lane].stream); continue; }
+      prev = k;
+      prev_lane = lane;
+    }
+    if (prev >= 0) { const int r2 = drain(prev, prev_lane); if (r2 && !rc) rc = r2; }
+    {
+      std::lock_guard<std::mutex> lk(P.m);
+      if (rc && !P.rc) P.rc = rc;
+      if (--P.running == 0) P.done.notify_all();
+    }
+  }
+}
+
+static int pool_dispatch(b2g_ctx* c, int nsub, std::function<int(int, int)> issue, std::function<int(int, int)> drain) {
+  if (!c->pool) {
+    c->pool = new HostPool();
+    for (int t = 0; t < g_lanes; t++) c->pool->th.emplace_back(pool_thread, c, t, g_lanes);
+  }
+  for (int l = 0; l < 2 * g_lanes; l++)
+    for (auto& e : c->lanes[l].piece)
+      if (!e) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming | cudaEventBlockingSync));
+  HostPool& P = *c->pool;
+  std::lock_guard<std::mutex> lk(P.m);
+  P.issue = std::move(issue);
+  P.drain = std::move(drain);
+  P.nsub = nsub;
+  P.running = (int)P.th.size();
+  P.rc = 0;
+  P.gen++;
+  P.go.notify_all();
+  return 0;
+}
+
+static int pool_wait(b2g_ctx* c) {
+  HostPool& P = *c->pool;
+  std::unique_lock<std::mutex> lk(P.m);
+  P.done.wait(lk, [&] { return P.running == 0; });
+  return P.rc;
+}
+
+static void pool_destroy(b2g_ctx* c) {
+  if (!c->pool) return;
+  {
+    std::lock_guard<std::mutex> lk(c->pool->m);
+    c->pool->quit = true;
+    c->pool->go.notify_all();
+  }
+  for (auto& t : c->pool->th) t.join();
+  delete c->pool;
+  c->pool = nullptr;
+}
+
+// Caller memory -> the lane's pinned buffer -> device, the H2D copy of a piece overlapping the memcpy of the next one.
+struct StagedUpload {
+  Lane& L;
+  uint8_t* d_base;      // device address of region offset 0
+  size_t sent = 0, filled = 0;
+  int rc = 0;
+  static constexpr size_t kPiece = (size_t)2 << 20;
+  void put(size_t off, const void* src, size_t len) {
+    memcpy((uint8_t*)L.h_in.p + off, src, len);
+    filled = off + len;
+    if (filled - sent >= kPiece) flush();
+  }
+  void flush() {
+    if (filled > sent && !rc &&
+        cuda_fail(cudaMemcpyAsync(d_base + sent, (uint8_t*)L.h_in.p + sent, filled - sent, cudaMemcpyHostToDevice, L.stream),
+                  "cudaMemcpyAsync"))
+      rc = B2G_ERR_NO_DEVICE;
+    sent = filled;
+  }
+};
+
 int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_stream) {
   if (!c || (!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
   if (c->pend) return B2G_ERR_FAILURE;
@@ -727,7 +883,8 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
       take = (size_t)std::max(kHdrMin, std::min(avail, cb < kHdrMin ? kHdrExt : cb));  // INT32_MAX: trust the header
       if (avail != INT32_MAX) take = std::min(take, (size_t)avail);
       if (nb > 0 && nb <= chunks[i].dst_capacity) give = (size_t)nb;
-      if (bs > 0 && bs <= kMaxBlocksize) {
+      // only a header that can decode at all may size the work buffers (plan_one rejects the others per chunk)
+      if (bs > 0 && bs <= kMaxBlocksize && nb > 0 && bs <= nb && nb <= chunks[i].dst_capacity) {
         maxblock = std::max(maxblock, bs);
         const int ts = src[3];  // split blocks are stored as `typesize` streams (flag bit 4 clear)
         const bool split = !(src[2] & kFlagDontSplit) && !(src[2] & kFlagMemcpyed) && ts >= 1 && ts <= kMaxStreams;
@@ -767,11 +924,80 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
   if (int rc = c->h_desc_all.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
   c->last_ms[0] = c->last_ms[1] = 0;
-  c->pend_bounds = split_batch(pay);
+  const bool staged = batch_needs_staging(chunks, n);
+  c->pend_bounds = split_batch(pay, staged);
   const int nsub = (int)c->pend_bounds.size() - 1;
   if (int rc = ensure_sub_events(c, nsub)) return rc;
   DChunk* desc = (DChunk*)c->h_desc_all.p;
   DResult* res = (DResult*)c->h_res_all.p;
+  if (staged) {
+    // pageable caller memory: every sub-batch runs on a worker thread through its lane's pinned buffers
+    c->st_in_off = in_off; c->st_out_off = out_off; c->st_in_len = in_len; c->st_out_len = out_len;
+    const int zstd = any_zstd, blz = any_blosclz, mstream = std::max(maxstream, 1);
+    auto issue = [c, chunks, desc, res, zstd, blz, mstream](int k, int lane) -> int {
+      Lane& L = c->lanes[lane];
+      const std::vector<int>& ord = c->pend_order;
+      const std::vector<size_t>&in_off = c->st_in_off, &out_off = c->st_out_off, &in_len = c->st_in_len, &out_len = c->st_out_len;
+      const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
+      cudaStream_t s = L.stream;
+      const size_t in_lo = in_off[ord[lo]];
+      const size_t in_hi = in_off[ord[lo + cnt - 1]] + in_len[ord[lo + cnt - 1]];
+      if (int rc = L.h_in.ensure(in_hi - in_lo + 16)) return rc;
+      StagedUpload up{L, (uint8_t*)c->d_in.p + in_lo};
+      size_t out_lo = (size_t)-1, out_hi = 0;
+      for (int q = lo; q < lo + cnt; q++) {
+        const int i = ord[q];
+        DChunk& d = desc[q];
+        d.src = (const uint8_t*)c->d_in.p + in_off[i];
+        d.dst = (uint8_t*)c->d_out.p + out_off[i];
+        d.src_bytes = chunks[i].src_bytes == INT32_MAX ? (int32_t)in_len[i]
+                                                       : std::min<int32_t>(chunks[i].src_bytes, (int32_t)in_len[i]);
+        d.dst_cap = chunks[i].dst_capacity;
+        if (in_len[i]) up.put(in_off[i] - in_lo, chunks[i].src, in_len[i]);
+        if (out_len[i]) { out_lo = std::min(out_lo, out_off[i]); out_hi = std::max(out_hi, out_off[i] + out_len[i]); }
+      }
+      up.flush();
+      if (up.rc) return up.rc;
+      if (int rc = enqueue_decode(c, L, desc + lo, cnt, s, zstd, mstream, res + lo, blz)) return rc;
+      L.st_out_lo = out_lo;
+      L.st_piece = 1;
+      L.st_npieces = 0;
+      if (out_hi > out_lo) {
+        const size_t span = out_hi - out_lo;
+        if (int rc = L.h_out.ensure(span + 16)) return rc;
+        L.st_piece = std::max<size_t>((size_t)4 << 20, align_up((span + kStagePieces - 1) / kStagePieces, 4096));
+        for (size_t o = 0; o < span; o += L.st_piece, L.st_npieces++) {
+          CU(cudaMemcpyAsync((uint8_t*)L.h_out.p + o, (uint8_t*)c->d_out.p + out_lo + o, std::min(L.st_piece, span - o),
+                             cudaMemcpyDeviceToHost, s));
+          CU(cudaEventRecord(L.piece[L.st_npieces], s));
+        }
+      }
+      return 0;
+    };
+    auto drain = [c, chunks, res](int k, int lane) -> int {
+      Lane& L = c->lanes[lane];
+      const std::vector<int>& ord = c->pend_order;
+      const std::vector<size_t>&out_off = c->st_out_off, &out_len = c->st_out_len;
+      const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
+      CU(cudaEventSynchronize(L.res_ready));
+      int waited = 0;
+      for (int q = lo; q < lo + cnt; q++) {
+        const int i = ord[q];
+        chunks[i].status = res[q].status;
+        chunks[i].out_bytes = res[q].status < 0 ? 0 : res[q].out_bytes;
+        if (!out_len[i]) continue;
+        const size_t o = out_off[i] - L.st_out_lo;
+        const int last = (int)((o + out_len[i] - 1) / L.st_piece);
+        for (; waited <= last && waited < L.st_npieces; waited++) CU(cudaEventSynchronize(L.piece[waited]));
+        memcpy(chunks[i].dst, (uint8_t*)L.h_out.p + o, out_len[i]);
+      }
+      CU(cudaStreamSynchronize(L.stream));
+      return 0;
+    };
+    if (int rc = pool_dispatch(c, nsub, issue, drain)) return rc;
+    c->pend = chunks; c->pend_n = n; c->pend_kind = 3;
+    return 0;
+  }
   for (int k = 0; k < nsub; k++) {
     Lane& L = c->lanes[k % g_lanes];
     const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
@@ -836,7 +1062,8 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
   }
   if (int rc = c->d_in.ensure(in_total + 512)) return rc;
   if (int rc = c->d_out.ensure(out_total + 256)) return rc;
-  c->pend_bounds = split_batch(payload);
+  const bool staged = batch_needs_staging(chunks, n);
+  c->pend_bounds = split_batch(payload, staged);
   const int nsub = (int)c->pend_bounds.size() - 1;
   if (int rc = c->h_desc_all.ensure((sizeof(DChunk) + sizeof(int32_t)) * (size_t)n)) return rc;
   if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
@@ -849,6 +1076,72 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
   DResult* res = (DResult*)c->h_res_all.p;
   CInfo* ci = (CInfo*)c->h_cinfo_all.p;
   int32_t* base = (int32_t*)c->h_base_all.p;
+  if (staged) {
+    c->st_in_off = in_off;
+    auto issue = [c, chunks, desc, nb, res, ci, base](int k, int lane) -> int {
+      Lane& L = c->lanes[lane];
+      const std::vector<int>& ord = c->pend_order;
+      const std::vector<size_t>& in_off = c->st_in_off;
+      const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
+      cudaStream_t s = L.stream;
+      const size_t in_lo = in_off[ord[lo]];
+      const size_t in_hi = in_off[ord[lo + cnt - 1]] + (size_t)std::max(chunks[ord[lo + cnt - 1]].src_bytes, 0);
+      if (int rc = L.h_in.ensure(in_hi - in_lo + 16)) return rc;
+      StagedUpload up{L, (uint8_t*)c->d_in.p + in_lo};
+      size_t out_cap = 0;
+      for (int q = lo; q < lo + cnt; q++) {
+        const int i = ord[q];
+        DChunk& d = desc[q];
+        d.src = (const uint8_t*)c->d_in.p + in_off[i];
+        d.dst = (uint8_t*)c->d_out.p + c->pend_out_off[i];
+        d.src_bytes = chunks[i].src_bytes;
+        d.dst_cap = std::min(chunks[i].dst_capacity, std::max(chunks[i].src_bytes, 0) + B2G_MAX_OVERHEAD);
+        nb[q] = chunks[i].src_bytes;
+        if (chunks[i].src_bytes > 0) up.put(in_off[i] - in_lo, chunks[i].src, (size_t)chunks[i].src_bytes);
+        out_cap += align_up((size_t)std::max(d.dst_cap, 0) + 16, 16);
+      }
+      up.flush();
+      if (up.rc) return up.rc;
+      if (int rc = enqueue_compress(c, L, desc + lo, nb + lo, cnt, s, ci + lo, base + lo + k, res + lo)) return rc;
+      return L.h_out.ensure(out_cap + 16);
+    };
+    auto drain = [c, chunks, res](int k, int lane) -> int {
+      Lane& L = c->lanes[lane];
+      const std::vector<int>& ord = c->pend_order;
+      const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
+      cudaStream_t s = L.stream;
+      CU(cudaEventSynchronize(L.res_ready));             // the sizes are known: fetch the chunks, densely packed
+      size_t off = 0;
+      int np = 0;                                         // an event every ~1/8 of the chunks: copy out while the rest lands
+      const int per = std::max(1, (cnt + kStagePieces - 1) / kStagePieces);
+      L.st_loc.resize((size_t)cnt);
+      for (int q = lo; q < lo + cnt; q++) {
+        const int i = ord[q];
+        chunks[i].status = res[q].status;
+        chunks[i].out_bytes = res[q].status < 0 ? 0 : res[q].out_bytes;
+        L.st_loc[(size_t)(q - lo)] = off;
+        if (chunks[i].out_bytes > 0) {
+          CU(cudaMemcpyAsync((uint8_t*)L.h_out.p + off, (uint8_t*)c->d_out.p + c->pend_out_off[i], (size_t)chunks[i].out_bytes,
+                             cudaMemcpyDeviceToHost, s));
+          off += align_up((size_t)chunks[i].out_bytes, 16);
+        }
+        if ((q - lo + 1) % per == 0 || q + 1 == lo + cnt) CU(cudaEventRecord(L.piece[np++], s));
+      }
+      int waited = 0;
+      for (int q = lo; q < lo + cnt; q++) {
+        const int i = ord[q];
+        const int need = std::min((q - lo) / per, np - 1);
+        for (; waited <= need; waited++) CU(cudaEventSynchronize(L.piece[waited]));
+        if (chunks[i].out_bytes > 0)
+          memcpy(chunks[i].dst, (uint8_t*)L.h_out.p + L.st_loc[(size_t)(q - lo)], (size_t)chunks[i].out_bytes);
+      }
+      CU(cudaStreamSynchronize(s));
+      return 0;
+    };
+    if (int rc = pool_dispatch(c, nsub, issue, drain)) return rc;
+    c->pend = chunks; c->pend_n = n; c->pend_kind = 3;
+    return 0;
+  }
   for (int k = 0; k < nsub; k++) {
     Lane& L = c->lanes[k % g_lanes];
     const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
@@ -888,6 +1181,7 @@ static int wait_host_batch(b2g_ctx* c) {
   const int kind = c->pend_kind;
   c->pend = nullptr;
   c->pend_kind = 0;
+  if (kind == 3) return pool_wait(c);   // staged: the worker threads have filled status / out_bytes
   const int nsub = (int)c->pend_bounds.size() - 1;
   const DResult* r = (const DResult*)c->h_res_all.p;
   int rc_all = 0;
@@ -1003,7 +1297,7 @@ b2g_ctx* b2g_clone(const b2g_ctx* c) {
   return b2g_create(&p);
 }
 
-int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }
+int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches.load() : (int64_t)0; }
 
 int b2g_last_kernel_ms(const b2g_ctx* c, float out_ms[2]) {
   if (!c || !out_ms) return B2G_ERR_INVALID_PARAM;

@@ -4,8 +4,9 @@ the data path.
 Every blosc2 chunk is self-describing and independent, so compress / decompress / get_chunk / set_chunk need no exchange:
 a batch is flattened to chunks, every rank takes one contiguous range balanced by bytes and runs its own b2g context on
 its own GPU.  The single exchange step is `get_decompressed()` of a channel whose chunks live on several GPUs: each rank
-decodes its range into its slice of a flat buffer and ONE all-gather (NCCL over NVLink on the GPU box; any
-torch.distributed backend works, the CPU tests use gloo) assembles the channel.  The reference has nothing comparable
+decodes its range into its slice of a flat buffer -- on a GPU box a DEVICE buffer, decoded in place by a device-resident batch --
+and ONE all-gather (NCCL over NVLink on the GPU box; any torch.distributed backend works, the CPU tests use gloo)
+assembles the channel.  The reference has nothing comparable
 (single process, compressed_image/include/compressed/channel.h:539-566 decodes the chunks in a loop).
 """
 import numpy as np
@@ -48,13 +49,14 @@ class ShardedChannel:
     decompress of the local engine (Channel._ctx().decompress on a GPU box); `encode(arrays)` the batched compress.
     """
 
-    def __init__(self, chunk_nbytes, rank, world, decode, encode=None, group=None):
+    def __init__(self, chunk_nbytes, rank, world, decode, encode=None, group=None, decode_device=None):
         self.chunk_nbytes = [int(b) for b in chunk_nbytes]
         self.rank, self.world = int(rank), int(world)
         self.ranges = shard_ranges(self.chunk_nbytes, self.world)
         self.lo, self.hi = self.ranges[self.rank]
         self._decode, self._encode = decode, encode
         self._group = group
+        self._decode_device = decode_device
         self.local_chunks = [None] * (self.hi - self.lo)
 
     # ---- no-collective operations ------------------------------------------------------------------------------
@@ -98,25 +100,71 @@ class ShardedChannel:
         return out
 
     # ---- the one exchange step -----------------------------------------------------------------------------------
-    def get_decompressed(self, device=None):
-        """Every rank returns the whole channel as a flat uint8 array: local decode, then one all-gather of the
-        per-rank segments (padded to the longest one so a single all_gather_into_tensor moves everything)."""
+    def get_decompressed(self, device=None, decode_device=None, as_tensor=False):
+        """Every rank returns the whole channel as a flat uint8 array: local decode, then ONE all-gather of the per-rank
+        segments (padded to the longest one so a single all_gather_into_tensor moves everything).
+
+        On a GPU box pass `decode_device(chunks, device_ptrs)` (shard_channel does): the rank's chunks are decoded
+        straight INTO its slice of a device buffer and the all-gather (NCCL over NVLink) runs on device pointers; nothing
+        of the decoded data touches host memory before the gather.  Without it (CPU tests over gloo) the local decode
+        lands in host memory first.  `as_tensor` returns the gathered torch tensor (on `device`) instead of numpy."""
         import torch
         import torch.distributed as dist
 
         seg = [sum(self.chunk_nbytes[lo:hi]) for lo, hi in self.ranges]
         pad = max(max(seg), 1)
         dev = torch.device(device) if device is not None else torch.device("cpu")
-        mine = torch.zeros(pad, dtype=torch.uint8, device=dev)
-        local = self.decode_local()
-        if local.size:
-            mine[:local.size] = torch.from_numpy(local).to(dev)
-        if self.world == 1:
-            return mine[:seg[0]].cpu().numpy()
         gathered = torch.empty(pad * self.world, dtype=torch.uint8, device=dev)
-        dist.all_gather_into_tensor(gathered, mine, group=self._group)
+        mine = gathered[self.rank * pad:(self.rank + 1) * pad]       # decode in place: rank r's slice of the result
+        if decode_device is None:
+            decode_device = self._decode_device
+        if decode_device is not None and dev.type == "cuda" and self.hi > self.lo:
+            ptrs, o = [], 0
+            for b in self.chunk_nbytes[self.lo:self.hi]:
+                ptrs.append(mine.data_ptr() + o)
+                o += b
+            decode_device(self.local_chunks, ptrs, self.chunk_nbytes[self.lo:self.hi])
+        else:
+            local = self.decode_local()
+            if local.size:
+                mine[:local.size] = torch.from_numpy(local).to(dev)
+        if self.world > 1:
+            dist.all_gather_into_tensor(gathered, mine.clone() if dist.get_backend(self._group) == "gloo" else mine,
+                                        group=self._group)
+        if as_tensor:
+            if all(s == pad for s in seg):
+                return gathered
+            return torch.cat([gathered[r * pad:r * pad + seg[r]] for r in range(self.world)])
         g = gathered.cpu().numpy()
         return np.concatenate([g[r * pad:r * pad + seg[r]] for r in range(self.world)])
+
+
+def device_decoder(ctx):
+    """decode_device(chunks, device_ptrs, nbytes) on a _b2g.Context: compressed chunks (host numpy) are uploaded into one
+    device buffer, then decoded by ONE device-resident batch (b2g_decompress_batch_device) into the given device
+    addresses."""
+    from . import _b2g
+
+    def decode(chunks, ptrs, nbytes):
+        import torch
+        sizes = [int(c.size) for c in chunks]
+        offs, total = [], 0
+        for sz in sizes:
+            offs.append(total)
+            total += (sz + 255) // 256 * 256
+        host = torch.empty(max(total, 1), dtype=torch.uint8).pin_memory()
+        hv = host.numpy()
+        for c, o, sz in zip(chunks, offs, sizes):
+            hv[o:o + sz] = c
+        dev = host.cuda(non_blocking=True)
+        b = ctx.make_batch([dev.data_ptr() + o for o in offs], list(ptrs), sizes, [int(x) for x in nbytes])
+        stream = torch.cuda.current_stream()
+        ctx.decompress_batch_device(b, stream=stream.cuda_stream)
+        ctx.wait()
+        for i in range(len(chunks)):
+            if b[i].status < 0:
+                raise _b2g.B2GError(b[i].status, "decompress chunk %d" % i)
+    return decode
 
 
 def shard_channel(channel, rank, world, group=None):
@@ -125,6 +173,6 @@ def shard_channel(channel, rank, world, group=None):
     ctx = channel._ctx()
     nbytes = [channel._nbytes_of(i) for i in range(channel.num_chunks())]
     sc = ShardedChannel(nbytes, rank, world, decode=lambda cs, outs: ctx.decompress(cs, outs),
-                        encode=lambda arrs: ctx.compress(arrs), group=group)
+                        encode=lambda arrs: ctx.compress(arrs), group=group, decode_device=device_decoder(ctx))
     sc.local_chunks = channel.chunks()[sc.lo:sc.hi]
     return sc
