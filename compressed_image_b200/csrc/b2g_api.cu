@@ -294,7 +294,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   // each of the two kernels; everything but the slots is zeroed per batch
   const int64_t pair_cap = c->pair_planes ? std::min<int64_t>(item_cap, (int64_t)1 << 24) : 0;
   const int nslots = 2048;
-  const size_t slot_bytes = (size_t)g.wcap;
+  const size_t slot_bytes = align_up((size_t)g.wcap, 128);   // whole 128-byte lines: the reader discards them from L2
   const size_t pair_ints = (size_t)nslots + 4 * (size_t)pair_cap;
   if (pair_cap > 0) {
     if (int rc = L.d_stage.ensure((size_t)nslots * slot_bytes)) return rc;

@@ -431,6 +431,17 @@ __device__ __forceinline__ void pair_planes(const DecodeArgs& a, const StreamJob
       }
     }
     if (lane == 0) atomicAdd(&a.ctl->paired, 1);
+    // The parked planes have been read for the last time: tell L2 so.  Without this every staged plane is written back
+    // to HBM once it ages out of the cache (measured: 53 MB of extra DRAM writes for 268 MB of output).
+#ifndef B2G_SIM
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (k < ns && k != s && (((uintptr_t)pl[k]) & 127) == 0) {
+        for (int o = lane * 128; o + 128 <= neblock; o += 32 * 128)
+          asm volatile("discard.global.L2 [%0], 128;" ::"l"(pl[k] + o) : "memory");
+      }
+    }
+#endif
   } else {
     scatter_plane(jb.raw, ns, s, win, neblock, lane);
 #pragma unroll

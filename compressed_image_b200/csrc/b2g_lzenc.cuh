@@ -24,7 +24,9 @@
 
 namespace b2g {
 
-constexpr int kEncTile = 1024;                 // positions per tile = 32 groups of 32 (one flag word per lane)
+constexpr int kEncTile = 512;                  // positions per tile = kEncGroups groups of 32 (the flag word of group g
+                                               // lives in lane g): 512 and not 1024 so that ten warps fit an SM
+constexpr int kEncGroups = kEncTile / 32;
 constexpr int kEncMaxSeq = kEncTile / 4;       // every sequence consumes >= 4 positions of its tile
 // per-warp work area after the hash table: off[kEncTile] u16, sp[kEncMaxSeq] u32, sml[kEncMaxSeq] u32, so[kEncMaxSeq] u16
 constexpr int kEncWorkBytes = kEncTile * 2 + kEncMaxSeq * 4 * 2 + kEncMaxSeq * 2;
@@ -95,15 +97,15 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
     // The equal-hash resolution (__match_any_sync) has a long latency and depends only on the input bytes, not on the
     // table: it is issued one step ahead, so that it completes under the previous step's verification work.
     unsigned myflags = 0;
-    auto next_step = [&](int gb) {  // first step at or after gb that has to be probed, 32 = none
-      for (; gb < 32; gb += 4) {
+    auto next_step = [&](int gb) {  // first step at or after gb that has to be probed, kEncGroups = none
+      for (; gb < kEncGroups; gb += 4) {
         const int bbase = tbase + gb * 32;
-        if (bbase > plimit) return 32;
+        if (bbase > plimit) return kEncGroups;
         if (bbase + 127 < ip) continue;
         if (step > 1 && ((gb >> 2) & (step - 1))) continue;
         return gb;
       }
-      return 32;
+      return kEncGroups;
     };
     uint32_t seq[4], h[4], nseqv[4], nh[4];
     unsigned peers[4], npeers[4];
@@ -121,13 +123,13 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       for (int j = 0; j < 4; j++) fp[j] = match_any_u32(fl[j] ? fh[j] : (0x80000000u | (uint32_t)lane));
     };
     int gb = next_step(0);
-    if (gb < 32) fetch(gb, nseqv, nh, npeers, nlive);
-    while (gb < 32) {
+    if (gb < kEncGroups) fetch(gb, nseqv, nh, npeers, nlive);
+    while (gb < kEncGroups) {
       const int bbase = tbase + gb * 32;
 #pragma unroll
       for (int j = 0; j < 4; j++) { seq[j] = nseqv[j]; h[j] = nh[j]; peers[j] = npeers[j]; live[j] = nlive[j]; }
       const int gbn = next_step(gb + 4);
-      if (gbn < 32) fetch(gbn, nseqv, nh, npeers, nlive);
+      if (gbn < kEncGroups) fetch(gbn, nseqv, nh, npeers, nlive);
       uint32_t tab[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) tab[j] = w.htab[h[j]];

@@ -140,27 +140,33 @@ class ShardedChannel:
 
 
 def device_decoder(ctx):
-    """decode_device(chunks, device_ptrs, nbytes) on a _b2g.Context: compressed chunks (host numpy) are uploaded into one
-    device buffer, then decoded by ONE device-resident batch (b2g_decompress_batch_device) into the given device
-    addresses."""
+    """decode_device(chunks, device_ptrs, nbytes) on a _b2g.Context: the compressed chunks (host numpy) are uploaded into
+    one device buffer ONCE -- a sharded channel keeps its range of chunk bytes resident in HBM until a chunk changes --
+    and decoded by ONE device-resident batch (b2g_decompress_batch_device) into the given device addresses."""
     from . import _b2g
+    cache = {}
 
     def decode(chunks, ptrs, nbytes):
         import torch
-        sizes = [int(c.size) for c in chunks]
-        offs, total = [], 0
-        for sz in sizes:
-            offs.append(total)
-            total += (sz + 255) // 256 * 256
-        host = torch.empty(max(total, 1), dtype=torch.uint8).pin_memory()
-        hv = host.numpy()
-        for c, o, sz in zip(chunks, offs, sizes):
-            hv[o:o + sz] = c
-        dev = host.cuda(non_blocking=True)
+        key = tuple(id(c) for c in chunks)
+        if cache.get("key") != key:
+            sizes = [int(c.size) for c in chunks]
+            offs, total = [], 0
+            for sz in sizes:
+                offs.append(total)
+                total += (sz + 255) // 256 * 256
+            host = torch.empty(max(total, 1), dtype=torch.uint8).pin_memory()
+            hv = host.numpy()
+            for c, o, sz in zip(chunks, offs, sizes):
+                hv[o:o + sz] = c
+            dev = host.cuda(non_blocking=True)
+            torch.cuda.current_stream().synchronize()  # the batch runs on the context's own stream: the upload has landed
+            cache.update(key=key, keep=list(chunks), dev=dev, offs=offs, sizes=sizes)
+        dev, offs, sizes = cache["dev"], cache["offs"], cache["sizes"]
+        torch.cuda.current_stream().synchronize()      # whatever the caller enqueued on the destination is done
         b = ctx.make_batch([dev.data_ptr() + o for o in offs], list(ptrs), sizes, [int(x) for x in nbytes])
-        stream = torch.cuda.current_stream()
-        ctx.decompress_batch_device(b, stream=stream.cuda_stream)
-        ctx.wait()
+        ctx.decompress_batch_device(b)
+        ctx.wait()                                     # ... and the decoded bytes are there before the caller's all-gather
         for i in range(len(chunks)):
             if b[i].status < 0:
                 raise _b2g.B2GError(b[i].status, "decompress chunk %d" % i)
