@@ -9,6 +9,8 @@ Same names, argument meaning and error behaviour as the reference: size mismatch
 (std::invalid_argument through pybind11), bad chunk indices IndexError (std::out_of_range), codec failures and
 constructor size mismatches RuntimeError (std::runtime_error).
 """
+import threading
+
 import numpy as np
 
 from . import _b2g
@@ -21,17 +23,23 @@ DEFAULT_CHUNKSIZE = 4_194_304     # compressed::s_default_chunksize (constants.h
 _DTYPES = tuple(np.dtype(t) for t in (np.uint8, np.int8, np.uint16, np.int16, np.uint32, np.int32, np.float16,
                                       np.float32))
 
-_ctx_pool = {}
+_ctx_tls = threading.local()
 
 
 def _context(codec, clevel, typesize, filt, blocksize, device=-1):
     """Contexts own device scratch + pinned staging, so they are pooled per parameter set rather than created per
-    channel / per get_chunk as the reference does with blosc2 contexts (channel.h:511-514)."""
+    channel / per get_chunk as the reference does with blosc2 contexts (channel.h:511-514).  A b2g_ctx is not
+    thread-safe (b2g.h) and ctypes releases the GIL during calls, so the pool is PER THREAD: two threads working on
+    different channels never meet in one context -- the reference gives every channel its own blosc2 contexts, which
+    makes per-channel threading safe there too."""
+    pool = getattr(_ctx_tls, "pool", None)
+    if pool is None:
+        pool = _ctx_tls.pool = {}
     key = (int(codec), int(clevel), int(typesize), int(filt), int(blocksize), int(device))
-    ctx = _ctx_pool.get(key)
+    ctx = pool.get(key)
     if ctx is None:
         ctx = _b2g.Context(*key)
-        _ctx_pool[key] = ctx
+        pool[key] = ctx
     return ctx
 
 
@@ -109,6 +117,7 @@ class Channel:
         if data.size != self._width * self._height:   # channel.h:113-123 throws std::runtime_error
             raise RuntimeError("Invalid channel data passed. Expected its size to match up to width * height (%d) but "
                              "instead got %d" % (self._width * self._height, data.size))
+        self._check_encoder()
         flat = np.ascontiguousarray(data).reshape(-1).view(np.uint8)
         cb = self._chunk_bytes
         pieces = [flat[o:o + cb] for o in range(0, flat.size, cb)]
@@ -126,6 +135,18 @@ class Channel:
         self._chunk_size_arg = int(chunk_size)
         self._chunk_bytes = align_chunk_to_scanlines_bytes(self._width, chunk_size, self._dtype.itemsize)
         self._chunks = []
+
+    def _check_encoder(self):
+        """The engine encodes blosclz, lz4 and lz4hc (as LZ4 streams); zstd chunks are decode-only.
+        Fail where the channel is built, not deep inside a batch."""
+        if self._codec == Codec.zstd:
+            raise RuntimeError("compressed_image_b200 has no zstd encoder (zstd chunks produced elsewhere decode bit-exactly); "
+                               "use Codec.lz4, Codec.lz4hc or Codec.blosclz to compress")
+        ts = self._dtype.itemsize                      # split rule of stune.c:200-209
+        split = (self._codec in (Codec.lz4, Codec.blosclz) and self._filter == _b2g.SHUFFLE and self._block_size // ts >= 32)
+        if self._block_size // (ts if split else 1) > 192 * 1024:
+            raise RuntimeError("block_size %d gives streams larger than the 192 KiB encoder window of this engine"
+                               % self._block_size)
 
     def _ctx(self):
         return _context(self._codec.blosc2_id, self._level, self._dtype.itemsize, self._filter, self._block_size,
@@ -267,6 +288,7 @@ class Channel:
         if array.size * self._dtype.itemsize != self._nbytes_of(i):   # schunk_mixin.h:216-246 -> std::invalid_argument
             raise ValueError("Invalid chunk size: expected %d elements, got %d" %
                              (self._nbytes_of(i) // self._dtype.itemsize, array.size))
+        self._check_encoder()
         self._chunks[i] = self._ctx().compress([array])[0]
 
     def set_chunks(self, chunk_indices, arrays):

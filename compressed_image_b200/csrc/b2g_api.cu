@@ -356,7 +356,9 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
 int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* nbytes, int n, cudaStream_t s,
                      CInfo* ci = nullptr, int32_t* base = nullptr, DResult* h_res = nullptr) {
   const b2g_params& p = c->p;
-  if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4) return B2G_ERR_CODEC_SUPPORT;  // encode: lz4 / blosclz only
+  // encode: blosclz, lz4, and lz4hc as plain LZ4 streams under the lz4hc codec id (unsplit blocks like the reference's,
+  // stune.c:200-209; the high-compression match search itself is not part of this build); no zstd encoder
+  if (p.codec != B2G_BLOSCLZ && p.codec != B2G_LZ4 && p.codec != B2G_LZ4HC) return B2G_ERR_CODEC_SUPPORT;
   if (p.typesize == 0) return B2G_ERR_INVALID_PARAM;
   if (p.clevel > 9) return B2G_ERR_CODEC_PARAM;
   if (!ci) {

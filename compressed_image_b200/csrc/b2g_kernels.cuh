@@ -706,7 +706,8 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
       uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
       const int cap = g.neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
       int n;
-      if (a.p.codec == kCodecLz4) n = lz_encode_warp<kCodecLz4>(win, g.neblock, out, cap, ew);
+      // lz4hc chunks hold ordinary LZ4 block streams (format id 1, blosc2.c:2457): the one LZ4 encoder writes both
+      if (a.p.codec == kCodecLz4 || a.p.codec == kCodecLz4hc) n = lz_encode_warp<kCodecLz4>(win, g.neblock, out, cap, ew);
       else n = lz_encode_warp<kCodecBlosclz>(win, g.neblock, out, cap, ew);
       if (n <= 0 || n >= g.neblock) { r.stored = 1; r.psize = r.csize = g.neblock; }
       else r.psize = r.csize = n;

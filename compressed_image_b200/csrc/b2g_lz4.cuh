@@ -111,15 +111,25 @@ __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8
     // ---- parse ahead ---------------------------------------------------------------------------------------------------
     while (!pstop) {
       // the usual sequence (at most one extension byte, on the literal length): nothing but the next token position
-      while (npend < 32) {
-        const uint32_t t = I.ld8(pip), e = I.ld8(pip + 1);
-        const uint32_t lit4 = t >> 4;
-        const bool l15 = lit4 == 15u;
-        const int q = pip + (int)lit4 + 3 + (l15 ? (int)e + 1 : 0);   // token, [extension], literals, offset
-        if ((t & 15u) == 15u || (l15 && e == 255u) || q > nlim) break;
-        if (lane == npend) tp = pip;
-        npend++;
-        pip = q;
+      // (the chain token load -> next position -> token load is what a noisy stream's time is made of: positions are
+      // absolute addresses of the view, both candidates for the next position hang off the loads side by side)
+      {
+        int base;
+        const auto A = I.origin(base);
+        int pa = base + pip;
+        const int alim = base + nlim;
+        while (npend < 32) {
+          const uint32_t t = A.ld8(pa), e = A.ld8(pa + 1);
+          const int q1 = pa + 3 + (int)(t >> 4);              // token, literals, offset
+          const int q2 = pa + 19 + (int)e;                    // token, extension byte, 15 + e literals, offset
+          const bool l15 = t >= 0xf0u;
+          const int q = l15 ? q2 : q1;
+          if ((t & 15u) == 15u || (l15 && e == 255u) || q > alim) break;
+          if (lane == npend) tp = pa - base;
+          npend++;
+          pa = q;
+        }
+        pip = pa - base;
       }
       if (npend == 32) break;
       // anything else: lengths with longer extensions; the end-of-stream rules (lz4.c:2279-2320) belong to the general path

@@ -22,6 +22,8 @@ struct MemGeneric {
   __device__ __forceinline__ uint32_t ld32(int i) const { return *(const uint32_t*)(p + i); }   // p + i word aligned
   __device__ __forceinline__ void st32(int i, uint32_t v) const { *(uint32_t*)(p + i) = v; }    // p + i word aligned
   __device__ __forceinline__ unsigned low2(int i) const { return (unsigned)((uintptr_t)(p + i) & 3); }
+  // a view whose index 0 is as cheap to address as it gets, and the index of this view's byte 0 in it
+  __device__ __forceinline__ MemGeneric origin(int& base) const { base = 0; return *this; }
 };
 
 #ifdef B2G_SIM
@@ -48,6 +50,8 @@ struct MemShared {
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(b + (uint32_t)i), "r"(v) : "memory");
   }
   __device__ __forceinline__ unsigned low2(int i) const { return (b + (uint32_t)i) & 3u; }
+  // indices of the returned view ARE shared-memory addresses: no add in front of a load whose index is a loop variable
+  __device__ __forceinline__ MemShared origin(int& base) const { base = (int)b; MemShared m(*this); m.b = 0; return m; }
 };
 #endif
 

@@ -46,7 +46,7 @@ enum {
   B2G_ERR_DATA = -3,            /* stream did not decode to exactly the expected size */
   B2G_ERR_READ_BUFFER = -5,     /* chunk truncated */
   B2G_ERR_WRITE_BUFFER = -6,    /* destination too small */
-  B2G_ERR_CODEC_SUPPORT = -7,   /* zlib / user codecs / dictionaries; encode with lz4hc or zstd */
+  B2G_ERR_CODEC_SUPPORT = -7,   /* zlib / user codecs / dictionaries; encode with zstd */
   B2G_ERR_CODEC_PARAM = -8,
   B2G_ERR_VERSION_SUPPORT = -10,
   B2G_ERR_INVALID_HEADER = -11,

@@ -286,3 +286,74 @@ def test_iterator_double_buffered_many_chunks():
         assert np.array_equal(x + 1, y)
         x[:] = y
     assert np.array_equal(np.asarray(a.get_decompressed()), np.asarray(b.get_decompressed()))
+
+
+# ---- round 2: codec coverage, threads, the headline config through the API ------------------------------------------
+def test_codec_lz4hc_roundtrip_and_zstd_refused_early():
+    """Channel(..., Codec.lz4hc) compresses (LZ4 streams under the lz4hc codec id, decodable by the reference);
+    Channel(..., Codec.zstd) is refused where the channel is built, with a message that says why (no zstd encoder)."""
+    c = _c()
+    data = _rand(np.uint16, (300, 512), seed=3)
+    ch = c.Channel(data, 512, 300, c.Codec.lz4hc, 5, chunk_size=64 * 512 * 2)
+    assert ch.compression() == c.Codec.lz4hc
+    assert np.array_equal(np.asarray(ch.get_decompressed()), data)
+    if _libs.ref() is not None:
+        for i, chunk in enumerate(ch.chunks()):
+            rc, back = _libs.ref_decompress(chunk)
+            assert rc == ch.chunk_size(i)
+    with pytest.raises(RuntimeError, match="zstd encoder"):
+        c.Channel(data, 512, 300, c.Codec.zstd)
+    lazy = c.Channel.zeros(np.uint16, 512, 300, c.Codec.zstd)      # lazy zstd channels exist, writing into them is refused
+    with pytest.raises(RuntimeError, match="zstd encoder"):
+        lazy.set_chunk(0, np.zeros(lazy.chunk_elems(0), np.uint16))
+    with pytest.raises(RuntimeError, match="encoder window"):
+        c.Channel(np.zeros((1024, 1024), np.uint8), 1024, 1024, block_size=512 * 1024)
+
+
+def test_channels_on_two_python_threads():
+    """ctypes releases the GIL during calls: two threads working on their own channels must not meet in one b2g_ctx
+    (the context pool is per thread)."""
+    import threading
+    c = _c()
+    errs = []
+
+    def work(seed):
+        try:
+            for k in range(6):
+                data = _rand(np.uint16, (600, 1024), seed=seed * 100 + k)
+                ch = c.Channel(data, 1024, 600, chunk_size=64 * 1024 * 2)
+                assert np.array_equal(np.asarray(ch.get_decompressed()), data)
+                ch.set_chunk(1, np.full(ch.chunk_elems(1), seed, np.uint16))
+                assert (ch.get_chunk(1) == seed).all()
+        except Exception as e:   # noqa: BLE001
+            errs.append(repr(e))
+    ts = [threading.Thread(target=work, args=(s,)) for s in range(4)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+
+
+def test_cfg2_random_access_through_the_api():
+    """BASELINE.json configs[1] through Channel itself: one 8192x4096 half channel (16 chunks of 4 MiB) and its alpha
+    channel, get_chunk over all chunks in a seeded random order, set_chunk of modified chunks, get_decompressed."""
+    c = _c()
+    from compressed_image_b200 import synth
+    w, h = 8192, 4096
+    for channel in (0, 3):
+        a = synth.half_channel(w, h, channel)
+        ch = c.Channel(a, w, h)
+        assert ch.num_chunks() == 16 and ch.chunk_size() == 4 << 20
+        flat = a.reshape(-1).copy()
+        per = ch.chunk_elems()
+        order = np.random.default_rng(1234).permutation(16)
+        for i in order:
+            got = ch.get_chunk(int(i))
+            assert np.array_equal(got.view(np.uint16), flat[i * per:(i + 1) * per].view(np.uint16))
+        for i in order[:8]:
+            new = (flat[i * per:(i + 1) * per].astype(np.float32) * 0.5).astype(np.float16)
+            ch.set_chunk(int(i), new)
+            flat[i * per:(i + 1) * per] = new
+        out = np.asarray(ch.get_decompressed()).reshape(-1)
+        assert np.array_equal(out.view(np.uint16), flat.view(np.uint16))

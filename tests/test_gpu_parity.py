@@ -229,14 +229,34 @@ def test_compress_capacity_rules():
 
 
 def test_unsupported_encoders_fail_loudly():
-    """zstd / lz4hc ENCODE is out of scope: the call fails, it does not fall back to a CPU."""
+    """zstd ENCODE is out of scope: the call fails, it does not fall back to a CPU."""
     from compressed_image_b200 import _b2g
     g = _gpu()
     src = _data.make_data("text", 50000, 1)
-    for codec in (_data.ZSTD, _data.LZ4HC):
-        with pytest.raises(_b2g.B2GError) as e:
-            g.compress_batch([src], codec, 5, 1, _data.SHUFFLE, 32768)
-        assert e.value.code == -7
+    with pytest.raises(_b2g.B2GError) as e:
+        g.compress_batch([src], _data.ZSTD, 5, 1, _data.SHUFFLE, 32768)
+    assert e.value.code == -7
+
+
+@pytest.mark.parametrize("ts", [1, 2, 4])
+def test_lz4hc_codec_id_encodes_as_lz4_streams(ts):
+    """Codec lz4hc: the chunks carry compcode 2 / format 1 and unsplit blocks, like the reference's lz4hc chunks
+    (stune.c:200-209, blosc2.c:2457); the streams are plain LZ4, which is what lz4hc streams are.  The reference and the
+    oracle decode them."""
+    g = _gpu()
+    srcs = [_data.make_data(k, 300000 + 8 * i, ts, seed=i) for i, k in enumerate(("half", "text", "sparse", "zeros", "random"))]
+    for (st, chunk), src in zip(g.compress_batch(srcs, _data.LZ4HC, 9, ts, _data.SHUFFLE, 32768), srcs):
+        assert st == 0
+        raw = src.reshape(-1).view(np.uint8)
+        if chunk[2] & 0x02 or chunk.size == 32:      # memcpyed / special chunk
+            pass
+        else:
+            assert chunk[22] == 2 and (chunk[2] >> 5) == 1 and (chunk[2] & 0x10), "lz4hc header fields"
+        rc, back = _checker_decompress(chunk)
+        assert rc == raw.size and np.array_equal(back, raw)
+    outs = g.decompress_batch([c for _, c in g.compress_batch(srcs, _data.LZ4HC, 9, ts, _data.SHUFFLE, 32768)])
+    for (st, out), src in zip(outs, srcs):
+        assert st == 0 and np.array_equal(out, src.reshape(-1).view(np.uint8))
 
 
 def test_async_host_batches_on_two_contexts():
