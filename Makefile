@@ -19,5 +19,7 @@ clean:
 # C++20 host layer check: the reference's OIIO-free test cases on include/compressed/*.h + libb2g.so
 CPPTEST := tests/cpp/test_compressed
 cpptest: $(CPPTEST)
-$(CPPTEST): tests/cpp/test_compressed.cpp $(wildcard include/compressed/*.h include/compressed/blosc2/*.h) include/b2g.h $(OUT)
-	g++ -std=c++20 -O2 -Wall -Wextra -Iinclude -o $@ tests/cpp/test_compressed.cpp -Lcompressed_image_b200 -lb2g -Wl,-rpath,'$$ORIGIN/../../compressed_image_b200'
+# nlohmann/json.hpp (image<T>::metadata) from wherever this image has one; without it the accessors are left out
+JSON_INC := $(firstword $(wildcard /opt/prime-rl/.venv/lib/python3.12/site-packages/include/cudnn_frontend/thirdparty /root/reference/thirdparty/json/include))
+$(CPPTEST): tests/cpp/test_compressed.cpp $(wildcard include/compressed/*.h include/compressed/*/*.h) include/b2g.h $(OUT)
+	g++ -std=c++20 -O2 -Wall -Wextra -Iinclude $(if $(JSON_INC),-I$(JSON_INC)) -o $@ tests/cpp/test_compressed.cpp -Lcompressed_image_b200 -lb2g -Wl,-rpath,'$$ORIGIN/../../compressed_image_b200'

@@ -69,6 +69,53 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 				}
 			}
 
+			/// The two halves of the constructor above, for callers that put the chunks of SEVERAL super-chunks into one
+			/// launch (compressed::image<T>: every channel of the image): plan() sizes the output buffers and appends one
+			/// job per chunk to `jobs`; after blosc2::compress_batch() over the combined list, adopt() takes this
+			/// super-chunk's `count` results starting at jobs[first].
+			struct compress_plan
+			{
+				std::vector<std::vector<std::byte>> buffers;
+				std::size_t first = 0, count = 0;
+			};
+			compress_plan plan(std::span<const T> data, std::vector<compress_job<T>>& jobs) const
+			{
+				compress_plan pl;
+				pl.first = jobs.size();
+				const std::size_t per_chunk = m_ChunkSize / sizeof(T);
+				for (std::size_t offset = 0; offset < data.size(); offset += per_chunk)
+				{
+					const std::size_t count = std::min(per_chunk, data.size() - offset);
+					pl.buffers.emplace_back(blosc2::min_compressed_size(count * sizeof(T)));
+					jobs.push_back({ data.subspan(offset, count), std::span<std::byte>(pl.buffers.back()), 0 });
+				}
+				pl.count = jobs.size() - pl.first;
+				return pl;
+			}
+			void adopt(compress_plan&& pl, std::span<const compress_job<T>> jobs)
+			{
+				for (std::size_t i = 0; i < pl.count; ++i)
+				{
+					pl.buffers[i].resize(jobs[pl.first + i].cbytes);
+					pl.buffers[i].shrink_to_fit();
+					m_Chunks.emplace_back(std::move(pl.buffers[i]));
+				}
+			}
+			/// One decompress job per stored chunk of this super-chunk into consecutive pieces of `out` (lazy chunks are
+			/// filled on the spot); the caller runs blosc2::decompress_batch() over the combined list.
+			void collect_decompress(std::span<T> out, std::vector<decompress_job<T>>& jobs) const
+			{
+				std::size_t offset = 0;
+				for (std::size_t i = 0; i < m_Chunks.size(); ++i)
+				{
+					const std::size_t count = this->chunk_elements(i);
+					auto piece = out.subspan(offset, count);
+					if (const auto* lazy = std::get_if<lazy_chunk>(&m_Chunks[i])) std::fill(piece.begin(), piece.end(), lazy->value);
+					else jobs.push_back({ piece, std::span<const std::byte>(std::get<0>(m_Chunks[i])), 0 });
+					offset += count;
+				}
+			}
+
 			/// `num_elements` copies of `value`, never compressed until written (lazyschunk.h:82-105).
 			schunk(T value, std::size_t num_elements, std::size_t block_size, std::size_t chunk_size)
 				: m_BlockSize(block_size), m_ChunkSize(chunk_size)

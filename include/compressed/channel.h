@@ -257,6 +257,7 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 	template <typename T>
 	struct channel
 	{
+		using value_type = T;
 		using iterator = channel_iterator<T>;
 
 		channel(channel&&) = default;
@@ -288,6 +289,33 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 			const std::size_t chunk_size_aligned = util::align_chunk_to_scanlines_bytes<T>(width, chunk_size);
 			m_Schunk = std::make_unique<blosc2::schunk<T>>(data, block_size, chunk_size_aligned, m_CompressionContext);
 		}
+
+		/// The constructor above in two steps, for compressed::image<T>, which compresses the chunks of ALL its channels
+		/// with one launch: deferred() validates and sets the channel up without compressing, plan_compress() appends
+		/// the channel's chunk jobs to the image-wide list, adopt_compressed() takes the results.
+		struct deferred_t {};
+		channel(deferred_t, std::size_t data_size, std::size_t width, std::size_t height, enums::codec compression_codec,
+			std::uint8_t compression_level, std::size_t block_size, std::size_t chunk_size)
+			: m_Codec(compression_codec), m_CompressionLevel(util::ensure_compression_level(compression_level)),
+			  m_Width(width), m_Height(height), m_BlockSize(block_size)
+		{
+			if (data_size != width * height)
+			{
+				throw std::runtime_error("Invalid channel data passed. Expected its size to match up to width * height (" +
+					std::to_string(width) + " * " + std::to_string(height) + ") which would be " +
+					std::to_string(width * height) + ". Instead got " + std::to_string(data_size));
+			}
+			create_contexts();
+			m_Schunk = std::make_unique<blosc2::schunk<T>>(block_size, util::align_chunk_to_scanlines_bytes<T>(width, chunk_size));
+		}
+		typename blosc2::schunk<T>::compress_plan plan_compress(std::span<const T> data,
+			std::vector<blosc2::compress_job<T>>& jobs) const { return m_Schunk->plan(data, jobs); }
+		void adopt_compressed(typename blosc2::schunk<T>::compress_plan&& pl, std::span<const blosc2::compress_job<T>> jobs)
+		{
+			m_Schunk->adopt(std::move(pl), jobs);
+		}
+		blosc2::context_raw_ptr compression_context() const noexcept { return m_CompressionContext.get(); }
+		blosc2::context_raw_ptr decompression_context() const noexcept { return m_DecompressionContext.get(); }
 
 		/// Adopt an existing super-chunk (channel.h:150-201).
 		channel(blosc2::schunk<T> schunk, std::size_t width, std::size_t height,

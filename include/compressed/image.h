@@ -3,13 +3,16 @@
 // The part of the reference's image<T> (compressed_image/include/compressed/image.h) that sits on the chunk path:
 // constructors from raw channel data (:87-258) and from channels (:276-325), channel() (:1192-1210), channels()
 // (:1289-1300), get_decompressed() (:1307-1315), add / remove / extract_channel (:940-1098), the size / ratio getters
-// (:1160-1175, 1339-1445) and update_nthreads (:1399-1405).  Not provided: read() (OpenImageIO file decode, :360-896) and
-// the json metadata accessors -- neither is on the chunk path.
+// (:1160-1175, 1339-1445), print_statistics (:1122-1156), the metadata accessors (:1379-1394, when nlohmann/json.hpp is on
+// the include path) and update_nthreads (:1399-1405).  Not provided: read() (OpenImageIO file decode, :360-896), which is
+// not on the chunk path.
 //
-// Every channel's chunks are compressed / decompressed as one batch (one launch per channel).
+// The chunks of ALL channels of an image are compressed (constructor) / decompressed (get_decompressed) as ONE batch: one
+// launch per image, where the reference loops channel by channel, chunk by chunk (:119-159, :1307-1315).
 #pragma once
 
 #include <cstddef>
+#include <iostream>
 #include <optional>
 #include <span>
 #include <stdexcept>
@@ -18,6 +21,8 @@
 #include <vector>
 
 #include "channel.h"
+#include "fwd.h"
+#include "json_alias.h"
 
 namespace NAMESPACE_COMPRESSED_IMAGE
 {
@@ -39,17 +44,30 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 		{
 			init_names(channels.size(), std::move(channel_names));
 			const auto level = util::ensure_compression_level(compression_level);
+			// every chunk of every channel in one compress batch
+			std::vector<blosc2::compress_job<T>> jobs;
+			std::vector<typename blosc2::schunk<T>::compress_plan> plans;
 			for (std::size_t i = 0; i < channels.size(); ++i)
 			{
 				try
 				{
-					m_Channels.emplace_back(channels[i], width, height, compression_codec, level, block_size, chunk_size);
+					m_Channels.emplace_back(typename compressed::channel<T>::deferred_t{}, channels[i].size(), width, height,
+						compression_codec, level, block_size, chunk_size);
+					plans.push_back(m_Channels.back().plan_compress(channels[i], jobs));
 				}
 				catch (const std::exception& e)
 				{
 					throw std::runtime_error("Unable to construct channel '" + m_ChannelNames[i] + "' (index " +
 						std::to_string(i) + "): " + e.what());
 				}
+			}
+			if (!jobs.empty())
+			{
+				blosc2::compress_batch<T>(m_Channels.front().compression_context(), std::span<blosc2::compress_job<T>>(jobs));
+			}
+			for (std::size_t i = 0; i < m_Channels.size(); ++i)
+			{
+				m_Channels[i].adopt_compressed(std::move(plans[i]), std::span<const blosc2::compress_job<T>>(jobs));
 			}
 		}
 
@@ -138,12 +156,21 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 		std::vector<compressed::channel<T>>& channels() { return m_Channels; }
 		const std::vector<compressed::channel<T>>& channels() const { return m_Channels; }
 
-		/// image.h:1307-1315
+		/// image.h:1307-1315: every chunk of every channel in one decompress batch.
 		std::vector<std::vector<T>> get_decompressed() const
 		{
 			std::vector<std::vector<T>> result;
 			result.reserve(m_Channels.size());
-			for (const auto& ch : m_Channels) result.push_back(ch.get_decompressed());
+			std::vector<blosc2::decompress_job<T>> jobs;
+			for (const auto& ch : m_Channels)
+			{
+				result.emplace_back(ch.uncompressed_size());
+				ch.schunk().collect_decompress(std::span<T>(result.back()), jobs);
+			}
+			if (!jobs.empty())
+			{
+				blosc2::decompress_batch<T>(m_Channels.front().decompression_context(), std::span<blosc2::decompress_job<T>>(jobs));
+			}
 			return result;
 		}
 
@@ -157,17 +184,55 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 			throw std::invalid_argument("Unknown channelname '" + std::string(channelname) + "' encountered");
 		}
 
-		/// image.h:1160-1175
+		/// image.h:1160-1170, reproduced as it is: both sums start at 1 and the uncompressed one counts ELEMENTS, so for
+		/// sizeof(T) > 1 the figure is the byte ratio divided by sizeof(T) (the Python tests of the reference pin it).
 		double compression_ratio() const noexcept
 		{
-			std::size_t compressed = 0, uncompressed = 0;
+			std::size_t total_uncompressed = 1, total_compressed = 1;
 			for (const auto& ch : m_Channels)
 			{
-				compressed += ch.compressed_bytes();
-				uncompressed += ch.uncompressed_size() * sizeof(T);
+				total_compressed += ch.compressed_bytes();
+				total_uncompressed += ch.uncompressed_size();
 			}
-			return compressed ? static_cast<double>(uncompressed) / static_cast<double>(compressed) : 0.0;
+			return static_cast<double>(total_uncompressed) / static_cast<double>(total_compressed);
 		}
+
+		/// image.h:1122-1156: a summary on stdout (sizes as the reference prints them: compressed bytes, uncompressed
+		/// elements).
+		void print_statistics()
+		{
+			std::size_t compressed_size = 0, uncompressed_size = 0, num_chunks = 0;
+			for (const auto& ch : m_Channels)
+			{
+				compressed_size += ch.compressed_bytes();
+				uncompressed_size += ch.uncompressed_size();
+				num_chunks += ch.num_chunks();
+			}
+			std::cout << "Statistics for image buffer:\n";
+			std::cout << " Width:             " << m_Width << "\n";
+			std::cout << " Height:            " << m_Height << "\n";
+			std::cout << " Channels:          " << m_Channels.size() << "\n";
+			std::cout << " Channelnames:      [";
+			for (std::size_t i = 0; i < m_ChannelNames.size(); ++i) std::cout << (i ? ", " : "") << m_ChannelNames[i];
+			std::cout << "]\n";
+			std::cout << " --------------     \n";
+			std::cout << " Compressed Size:   " << compressed_size << "\n";
+			std::cout << " Uncompressed Size: " << uncompressed_size << "\n";
+			std::cout << " Compression ratio: " << static_cast<double>(uncompressed_size) / static_cast<double>(compressed_size) << "x\n";
+			std::cout << " Num Chunks:        " << num_chunks << "\n";
+#ifdef COMPRESSED_IMAGE_HAVE_JSON
+			std::cout << " Metadata:          \n " << m_Metadata.dump(4) << std::endl;
+#else
+			std::cout << " Metadata:          \n (nlohmann/json.hpp not on the include path)" << std::endl;
+#endif
+		}
+
+#ifdef COMPRESSED_IMAGE_HAVE_JSON
+		/// image.h:1379-1394: arbitrary user metadata, neither authored nor interpreted by the image.
+		void metadata(const json_ordered& _metadata) noexcept { m_Metadata = _metadata; }
+		json_ordered& metadata() noexcept { return m_Metadata; }
+		const json_ordered& metadata() const noexcept { return m_Metadata; }
+#endif
 
 		std::size_t width() const noexcept { return m_Width; }
 		std::size_t height() const noexcept { return m_Height; }
@@ -214,6 +279,9 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 
 		std::vector<compressed::channel<T>> m_Channels;
 		std::vector<std::string> m_ChannelNames;
+#ifdef COMPRESSED_IMAGE_HAVE_JSON
+		json_ordered m_Metadata;
+#endif
 		std::size_t m_Width = 1, m_Height = 1;
 	};
 }

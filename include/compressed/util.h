@@ -3,8 +3,11 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <memory>
 #include <stdexcept>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "macros.h"
 
@@ -12,6 +15,36 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 {
 	namespace util
 	{
+		namespace detail
+		{
+			/// Allocator whose construct() default-initialises: a vector of T resized to n does not zero its n elements.
+			template <typename T, typename A = std::allocator<T>>
+			struct default_init_allocator : public A
+			{
+				using A::A;
+				template <typename U>
+				struct rebind
+				{
+					using other = default_init_allocator<U, typename std::allocator_traits<A>::template rebind_alloc<U>>;
+				};
+				template <typename U>
+				void construct(U* ptr) noexcept(std::is_nothrow_default_constructible_v<U>)
+				{
+					::new (static_cast<void*>(ptr)) U;
+				}
+				template <typename U, typename... Args>
+				void construct(U* ptr, Args&&... args)
+				{
+					std::allocator_traits<A>::construct(static_cast<A&>(*this), ptr, std::forward<Args>(args)...);
+				}
+			};
+		}
+
+		/// util.h:56-57 -- a std::vector that skips value-initialisation on resize (scratch / swap buffers that are about to
+		/// be overwritten by a decompress batch anyway).
+		template <typename T>
+		using default_init_vector = std::vector<T, detail::default_init_allocator<T>>;
+
 		/// Clamp a compression level into blosc2's 0..9.
 		inline std::uint8_t ensure_compression_level(std::size_t level)
 		{

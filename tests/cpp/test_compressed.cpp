@@ -16,6 +16,16 @@
 
 #include "compressed/image.h"
 #include "compressed/image_algo.h"
+// the reference's include paths for the same things (forwarding headers)
+#include "compressed/blosc2/lazyschunk.h"
+#include "compressed/blosc2/schunk_mixin.h"
+#include "compressed/blosc2/typedefs.h"
+#include "compressed/blosc2/util.h"
+#include "compressed/containers/chunk_span.h"
+#include "compressed/fwd.h"
+#include "compressed/iterators/iterator.h"
+#include "compressed/json_alias.h"
+#include "compressed/ranges.h"
 
 static int g_failed = 0, g_checks = 0;
 #define CHECK(cond)                                                                      \
@@ -260,6 +270,55 @@ static void test_image_algo(size_t nch, size_t n)
 	}
 }
 
+// image<T>: one launch for the whole image (round 2), the statistics helpers of image.h:1122-1170, metadata, zip.
+static void test_image_batched()
+{
+	const size_t w = 256, h = 128, nch = 5;
+	std::vector<std::vector<uint16_t>> data(nch, std::vector<uint16_t>(w * h));
+	for (size_t c = 0; c < nch; ++c)
+		for (size_t i = 0; i < w * h; ++i) data[c][i] = static_cast<uint16_t>((i / 7 + c * 31) & 0x3ff);
+	ci::image<uint16_t> img(data, w, h, { "R", "G", "B", "A", "Z" }, ci::enums::codec::lz4, 9, 32768, 16 * w * sizeof(uint16_t));
+	CHECK(img.num_channels() == nch);
+	CHECK(img.channel(0).num_chunks() == h / 16);
+	// all 5 x 8 chunks went through the FIRST channel's context, as one batch: 3 kernels (compress, place, finalize) in
+	// the engine, 1 batch in the CPU mock the host-logic test links against
+	const bool mock = std::string(b2g_version()) == "mock";
+	CHECK(b2g_launch_count(img.channel(0).compression_context()) == (mock ? 1 : 3));
+	CHECK(b2g_launch_count(img.channel(1).compression_context()) == 0);
+	const auto back = img.get_decompressed();
+	CHECK(back.size() == nch);
+	for (size_t c = 0; c < nch; ++c) CHECK(back[c] == data[c]);
+	CHECK(b2g_launch_count(img.channel(0).decompression_context()) == (mock ? 1 : 2));   // plan + decode, once for the image
+	// compression_ratio(): the reference's arithmetic (both sums seeded with 1, uncompressed counted in elements)
+	size_t comp = 1, unc = 1;
+	for (const auto& ch : img.channels()) { comp += ch.compressed_bytes(); unc += ch.uncompressed_size(); }
+	CHECK(img.compression_ratio() == static_cast<double>(unc) / static_cast<double>(comp));
+	img.print_statistics();
+#ifdef COMPRESSED_IMAGE_HAVE_JSON
+	img.metadata({ { "author", "test" }, { "frame", 12 } });
+	CHECK(img.metadata()["author"] == "test");
+	CHECK(img.metadata().dump() == "{\"author\":\"test\",\"frame\":12}");      // ordered_json keeps insertion order
+#endif
+	// a lazy channel next to compressed ones
+	img.add_channel(ci::channel<uint16_t>::full(w, h, 7), "fill");
+	const auto back2 = img.get_decompressed();
+	CHECK(back2.size() == nch + 1 && back2[nch] == std::vector<uint16_t>(w * h, 7) && back2[2] == data[2]);
+	// ranges::zip: lock-step chunk iteration over two channels, modifications written back
+	auto& a = img.channel("R");
+	auto& b = img.channel("G");
+	size_t steps = 0;
+	for (auto [ca, cb] : ci::ranges::zip(a, b))
+	{
+		CHECK(ca.size() == cb.size());
+		for (size_t i = 0; i < ca.size(); ++i) ca[i] = cb[i];
+		++steps;
+	}
+	CHECK(steps == a.num_chunks());
+	CHECK(a.get_decompressed() == data[1]);
+	ci::blosc2::lazy_schunk<float> lazy(1.5f, 1000, 4096, 1024);
+	CHECK(lazy.num_chunks() == 4 && lazy.is_lazy(3));
+}
+
 int main()
 {
 	if (b2g_device_count() < 1)
@@ -286,6 +345,7 @@ int main()
 		test_image<uint8_t>(chunk); test_image<uint16_t>(chunk); test_image<float>(chunk);
 	}
 	test_iterator_pipeline();
+	test_image_batched();
 	for (size_t nch : { size_t(1), size_t(3), size_t(4), size_t(7), size_t(16) })
 	{
 		test_image_algo<uint8_t>(nch, 1000003); test_image_algo<uint16_t>(nch, 64 * 64);

@@ -67,3 +67,43 @@ def test_cpp_host_logic_against_deferred_mock(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert " 0 failed" in r.stdout
+
+
+REF = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "python", "bindings")), reason="the reference tree is not on this machine")
+def test_reference_channel_bindings_compile_against_these_headers(tmp_path):
+    """The drop-in claim of INTEGRATION.md, checked: the reference's own pybind11 channel bindings
+    (python/bindings/bind_channel.h, bind_enums.h, wrappers/dynamic_channel.h, util/*.h -- read where they lie, unmodified)
+    compile (g++ -std=c++20 -fsyntax-only) against include/compressed/*.h of THIS repo instead of the reference's headers.
+    Imath is not installed here: a test-only stand-in for Imath/half.h (a 16-bit storage type) is generated into tmp_path.
+    The image bindings (wrappers/dynamic_image.h) include OpenImageIO and pybind11_json unconditionally and call
+    image<T>::read: they cannot be compiled in this container against ANY headers, the reference's own included."""
+    try:
+        import pybind11
+    except ImportError:
+        pytest.skip("pybind11 not importable")
+    import sysconfig
+    shim = tmp_path / "Imath"
+    shim.mkdir()
+    (shim / "half.h").write_text(
+        "#pragma once\n#include <cstdint>\nnamespace Imath { struct half { std::uint16_t bits; half() = default; "
+        "half(float f) : bits(static_cast<std::uint16_t>(f)) {} operator float() const { return static_cast<float>(bits); } }; }\n"
+        "using half = Imath::half;\n")
+    tu = tmp_path / "tu.cpp"
+    tu.write_text('#include "bind_channel.h"\n#include "bind_enums.h"\nint main() { return 0; }\n')
+    cmd = ["g++", "-std=c++20", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(REF, "python", "bindings"),
+           "-I" + str(tmp_path), "-I" + pybind11.get_include(), "-I" + sysconfig.get_paths()["include"],
+           "-I" + os.path.join(REF, "thirdparty", "pybind11_image_util", "pybind11_image_util", "include"), str(tu)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-4000:]
+
+
+def test_forwarding_headers_cover_the_reference_include_paths():
+    """Every header the reference ships under compressed/ that belongs to the chunk path exists at the same path here."""
+    want = ["channel.h", "constants.h", "enums.h", "fwd.h", "image.h", "image_algo.h", "json_alias.h", "macros.h", "ranges.h",
+            "util.h", "blosc2/lazyschunk.h", "blosc2/schunk.h", "blosc2/schunk_mixin.h", "blosc2/typedefs.h", "blosc2/util.h",
+            "blosc2/wrapper.h", "containers/chunk_span.h", "iterators/iterator.h"]
+    for w in want:
+        assert os.path.exists(os.path.join(ROOT, "include", "compressed", w)), w
