@@ -274,7 +274,7 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
   int got;
   if (Z) {
     if (fmt != kFmtZstd) return kErrCodec;
-    long r = zstd_decode_warp(zw, payload, csize, win, neblock);
+    long r = zstd_decode_warp(zw, payload, csize, win, neblock, STAGE);   // STAGE: a window with slack, not the caller's buffer
     got = r < 0 ? 0 : (int)r;  // blosc2.c:545-548: zstd errors surface as 0 bytes
   } else {
     if (fmt != kFmtLz4 && fmt != kFmtBlosclz) return kErrCodec;

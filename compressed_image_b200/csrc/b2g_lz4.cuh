@@ -95,6 +95,76 @@ inline SimDecodeStats& sim_decode_stats() { static SimDecodeStats s = {0, 0, 0, 
 constexpr int kLitLane = 64;   // literal bytes a sequence's own lane copies
 constexpr int kMatLane = 32;   // longest match a lane copies on its own
 
+// Executes `cnt` decoded sequences at once, lane k < cnt holding sequence k: its literal run I[lpos .. lpos + lit) goes
+// to O[myop ..), its match of `ml` bytes from `off` back to O[cpy ..) (cpy = myop + lit; the next sequence's myop is
+// cpy + ml).  The caller has checked the bounds, that no destination of the batch reaches a literal source of the batch
+// (in-place windows), and that off <= cpy.  Shared by the LZ4 decoder and the zstd sequence executor.
+//   literals  every lane copies its own run (the first kLitLane bytes; the whole warp finishes longer runs).
+//   matches   a match whose source lies in bytes that no match of the same batch writes (literals of the batch or
+//             anything before it; found with a binary search over the lanes' output positions) is copied by its own
+//             lane, all of them at once; the others (and long ones) follow in stream order, copied by the whole warp.
+// off == 0 (LZ4 only: accepted by LZ4_decompress_safe, the match reads itself after lz4.c:500 / :2407 zeroed its first
+// word) produces zeros.
+template <class IN, class OUT>
+__device__ __forceinline__ void lz_batch_execute(const IN& I, const OUT& O, uint8_t* out, int lane, int cnt, int lpos,
+                                                 int myop, int lit, int cpy, int off, int ml) {
+  const bool exec = lane < cnt;
+  // ---- literals --------------------------------------------------------------------------------------------------------
+  lane_copy(I, lpos, O, myop, exec ? min(lit, kLitLane) : 0);
+  unsigned lm = __ballot_sync(kFull, exec && lit > kLitLane);
+  while (lm) {
+    const int j = __ffs((int)lm) - 1;
+    lm &= lm - 1;
+    const int sj = __shfl_sync(kFull, lpos, j) + kLitLane, dj = __shfl_sync(kFull, myop, j) + kLitLane;
+    warp_copy(I, sj, O, dj, __shfl_sync(kFull, lit, j) - kLitLane, lane);
+  }
+  __syncwarp();
+  // ---- matches ---------------------------------------------------------------------------------------------------------
+  const int s = cpy - off;                 // source start; the source ends at se or runs into the match itself
+  const int se = min(s + ml, cpy);
+  int j = 0;                               // the sequence whose output holds byte s (0: before the batch)
+#pragma unroll
+  for (int b = 16; b; b >>= 1) {
+    const int c = j + b;
+    const int v = __shfl_sync(kFull, myop, c & 31);
+    if (c < cnt && v <= s) j = c;
+  }
+  const int cj = __shfl_sync(kFull, cpy, j);   // [s, se) ends before that sequence's match: literals only
+  const bool par = exec && ml <= kMatLane && off != 0 && se <= cj;
+  // sources at least 4 bytes back: four bytes per step (loads first); closer ones: byte by byte, so that a source
+  // overlapping the match itself reads what the lane has just written
+  const int nm4 = par && off >= 4 ? ml : 0;
+  const int max4 = (int)__reduce_max_sync(kFull, (unsigned)nm4);
+  for (int i = 0; i < max4; i += 4) {
+    uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+    if (i < nm4) v0 = O.ld8(s + i);
+    if (i + 1 < nm4) v1 = O.ld8(s + i + 1);
+    if (i + 2 < nm4) v2 = O.ld8(s + i + 2);
+    if (i + 3 < nm4) v3 = O.ld8(s + i + 3);
+    if (i < nm4) O.st8(cpy + i, v0);
+    if (i + 1 < nm4) O.st8(cpy + i + 1, v1);
+    if (i + 2 < nm4) O.st8(cpy + i + 2, v2);
+    if (i + 3 < nm4) O.st8(cpy + i + 3, v3);
+  }
+  const int nm1 = par && off < 4 ? ml : 0;
+  const int max1 = (int)__reduce_max_sync(kFull, (unsigned)nm1);
+  for (int i = 0; i < max1; i++)
+    if (i < nm1) O.st8(cpy + i, O.ld8(s + i));
+  __syncwarp();
+  unsigned rest = __ballot_sync(kFull, exec && !par);
+  B2G_SIM_STAT(batches, 1);
+  B2G_SIM_STAT(batch_seqs, cnt);
+  B2G_SIM_STAT(ordered_matches, __popc(rest));
+  while (rest) {
+    const int k = __ffs((int)rest) - 1;
+    rest &= rest - 1;
+    const int c = __shfl_sync(kFull, cpy, k), o = __shfl_sync(kFull, off, k), m = __shfl_sync(kFull, ml, k);
+    if (o == 0) fill_bytes(out + c, 0, m, lane, 32);
+    else lz_match_copy(out, c, o, m, lane);
+    __syncwarp();
+  }
+}
+
 template <bool INPLACE, bool SMEM>
 __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8_t* out, int cap, int a) {
   const int lane = lane_id();
@@ -187,62 +257,7 @@ __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8
       if (cnt > 0) {
         const bool exec = lane < cnt;
         if (__any_sync(kFull, exec && off > cpy)) return -1;  // lz4.c:2356 offset beyond the start of the output
-        // ---- literals --------------------------------------------------------------------------------------------------
-        lane_copy(I, lpos, O, myop, exec ? min(lit, kLitLane) : 0);
-        unsigned lm = __ballot_sync(kFull, exec && lit > kLitLane);
-        while (lm) {
-          const int j = __ffs((int)lm) - 1;
-          lm &= lm - 1;
-          const int sj = __shfl_sync(kFull, lpos, j) + kLitLane, dj = __shfl_sync(kFull, myop, j) + kLitLane;
-          warp_copy(I, sj, O, dj, __shfl_sync(kFull, lit, j) - kLitLane, lane);
-        }
-        __syncwarp();
-        // ---- matches ---------------------------------------------------------------------------------------------------
-        {
-          const int s = cpy - off;                 // source start; the source ends at se or runs into the match itself
-          const int se = min(s + ml, cpy);
-          int j = 0;                               // the sequence whose output holds byte s (0: before the batch)
-#pragma unroll
-          for (int b = 16; b; b >>= 1) {
-            const int c = j + b;
-            const int v = __shfl_sync(kFull, myop, c & 31);
-            if (c < cnt && v <= s) j = c;
-          }
-          const int cj = __shfl_sync(kFull, cpy, j);   // [s, se) ends before that sequence's match: literals only
-          const bool par = exec && ml <= kMatLane && off != 0 && se <= cj;
-          // sources at least 4 bytes back: four bytes per step (loads first); closer ones: byte by byte, so that a source
-          // overlapping the match itself reads what the lane has just written
-          const int nm4 = par && off >= 4 ? ml : 0;
-          const int max4 = (int)__reduce_max_sync(kFull, (unsigned)nm4);
-          for (int i = 0; i < max4; i += 4) {
-            uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0;
-            if (i < nm4) v0 = O.ld8(s + i);
-            if (i + 1 < nm4) v1 = O.ld8(s + i + 1);
-            if (i + 2 < nm4) v2 = O.ld8(s + i + 2);
-            if (i + 3 < nm4) v3 = O.ld8(s + i + 3);
-            if (i < nm4) O.st8(cpy + i, v0);
-            if (i + 1 < nm4) O.st8(cpy + i + 1, v1);
-            if (i + 2 < nm4) O.st8(cpy + i + 2, v2);
-            if (i + 3 < nm4) O.st8(cpy + i + 3, v3);
-          }
-          const int nm1 = par && off < 4 ? ml : 0;
-          const int max1 = (int)__reduce_max_sync(kFull, (unsigned)nm1);
-          for (int i = 0; i < max1; i++)
-            if (i < nm1) O.st8(cpy + i, O.ld8(s + i));
-          __syncwarp();
-          unsigned rest = __ballot_sync(kFull, exec && !par);
-          B2G_SIM_STAT(batches, 1);
-          B2G_SIM_STAT(batch_seqs, cnt);
-          B2G_SIM_STAT(ordered_matches, __popc(rest));
-          while (rest) {
-            const int k = __ffs((int)rest) - 1;
-            rest &= rest - 1;
-            const int c = __shfl_sync(kFull, cpy, k), o = __shfl_sync(kFull, off, k), m = __shfl_sync(kFull, ml, k);
-            if (o == 0) fill_bytes(out + c, 0, m, lane, 32);  // accepted by LZ4_decompress_safe: the match reads itself
-            else lz_match_copy(out, c, o, m, lane);           // after lz4.c:500 / :2407 zeroed its first word -> zeros
-            __syncwarp();
-          }
-        }
+        lz_batch_execute(I, O, out, lane, cnt, lpos, myop, lit, cpy, off, ml);
         op = __shfl_sync(kFull, mend, cnt - 1);
         ip = __shfl_sync(kFull, nip, cnt - 1);
         tp = __shfl_down_sync(kFull, tp, (unsigned)cnt);

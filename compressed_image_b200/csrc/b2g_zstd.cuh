@@ -68,22 +68,47 @@ __device__ __forceinline__ uint32_t z_bits(const uint8_t* src, long n, long lo, 
   return (uint32_t)((v >> (lo & 7)) & ((1ull << nb) - 1));
 }
 
-struct ZBack {  // backward bit reader (common/bitstream.h:248-400)
+// Backward bit reader (common/bitstream.h:248-400).  `bits` counts the unread bits of the stream (negative = overrun,
+// exactly as before); the next `avail` of them sit left-aligned in the 64-bit container `cont`, so that a field costs a
+// shift and a mask, and memory is touched once per ~57 bits instead of once per field (the Huffman and FSE loops are
+// chains of dependent reads: the four loads + three funnel shifts of an unaligned 64-bit fetch per field were most of
+// their time).
+struct ZBack {
   const uint8_t* p;
   long n;
-  long bits;  // unread bits; negative = overrun
+  long bits;
+  uint64_t cont;
+  int avail;
 };
+__device__ __forceinline__ void zb_refill(ZBack& b) {
+  const long end = (b.bits + 7) >> 3;                       // first byte boundary at or above the read position
+  const int extra = (int)(end * 8 - b.bits);                // 0..7 bits of `end`'s byte are already consumed
+  const uint64_t v = z_ld64(b.p, b.n, end - 8);             // bytes below 0 read as zero
+  b.cont = v << extra;
+  b.avail = 64 - extra;
+}
 __device__ __forceinline__ bool zb_init(ZBack& b, const uint8_t* p, long n) {
   if (n < 1) return false;
   uint32_t last = p[n - 1];
   if (last == 0) return false;
   b.p = p; b.n = n;
   b.bits = n * 8 - (8 - z_hbit(last));
+  zb_refill(b);
   return true;
 }
-__device__ __forceinline__ uint32_t zb_read(ZBack& b, int nb) {
-  uint32_t v = z_bits(b.p, b.n, b.bits - nb, nb);
+// the next nb (<= 32) bits without consuming them
+__device__ __forceinline__ uint32_t zb_peek(ZBack& b, int nb) {
+  if (b.avail < nb) zb_refill(b);
+  return nb > 0 ? (uint32_t)(b.cont >> (64 - nb)) : 0u;
+}
+__device__ __forceinline__ void zb_skip(ZBack& b, int nb) {   // after zb_peek(b, >= nb)
+  b.cont <<= nb;
+  b.avail -= nb;
   b.bits -= nb;
+}
+__device__ __forceinline__ uint32_t zb_read(ZBack& b, int nb) {
+  const uint32_t v = zb_peek(b, nb);
+  zb_skip(b, nb);
   return v;
 }
 
@@ -262,11 +287,28 @@ __device__ __forceinline__ bool z_huf_stream(const ZWork* z, const uint8_t* src,
   ZBack b;
   if (!zb_init(b, src, n)) return false;
   const int log = z->huf_log;
-  for (long i = 0; i < count; i++) {
-    uint32_t idx = z_bits(b.p, b.n, b.bits - log, log);
-    uint32_t e = z->huf[idx];
+  long i = 0;
+  // four symbols per refill check: a symbol takes at most kZHufLogMax = 12 bits, a refilled container holds >= 57
+  for (; i + 4 <= count; i += 4) {
+    if (b.avail < 4 * kZHufLogMax) zb_refill(b);
+    uint64_t c = b.cont;
+    int used = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t e = z->huf[(uint32_t)(c >> (64 - log))];
+      const int nb = (int)(e >> 8);
+      out[i + k] = (uint8_t)e;
+      c <<= nb;
+      used += nb;
+    }
+    b.cont = c;
+    b.avail -= used;
+    b.bits -= used;
+  }
+  for (; i < count; i++) {
+    const uint32_t e = z->huf[zb_peek(b, log)];
     out[i] = (uint8_t)e;
-    b.bits -= (long)(e >> 8);
+    zb_skip(b, (int)(e >> 8));
   }
   return b.bits == 0;
 }
@@ -358,7 +400,7 @@ __device__ __forceinline__ void z_move_literals(uint8_t* dst, const uint8_t* src
 // One compressed block (ZSTD_decompressBlock_internal, zstd_decompress_block.c:2066-2200).  `win` = frame output
 // start, `op` = bytes already produced, cap = capacity.  Returns the new op or -1.
 __device__ __forceinline__ long z_decode_block(ZWork* z, const uint8_t* src, long n, uint8_t* win, long op, long cap,
-                                               long blockmax, int lane) {
+                                               long blockmax, int lane, bool batch) {
   long litsize = 0;
   long used = z_decode_literals(z, src, n, win, cap, op, &litsize, blockmax, lane);
   if (used < 0) return -1;
@@ -405,48 +447,113 @@ __device__ __forceinline__ long z_decode_block(ZWork* z, const uint8_t* src, lon
     uint32_t sl = zb_read(b, lllog), so = zb_read(b, oflog), sm = zb_read(b, mllog);
     if (b.bits < 0) return -1;
     uint32_t rep0 = z->rep[0], rep1 = z->rep[1], rep2 = z->rep[2];
-    for (long i = 0; i < nbseq; i++) {
-      const uint32_t el = z->ll[sl], eo = z->of[so], em = z->ml[sm];
-      const uint32_t llc = el & 0xff, ofc = eo & 0xff, mlc = em & 0xff;
-      if (llc > kZMaxLL || mlc > kZMaxML || ofc > kZMaxOff) return -1;
-      const uint32_t ll_base = kZLLBase[llc];
-      uint32_t offset;
-      if (ofc > 1) {
-        offset = ((1u << ofc) - 3) + zb_read(b, (int)ofc);
-        rep2 = rep1; rep1 = rep0; rep0 = offset;
-      } else {
-        const uint32_t ll0 = (ll_base == 0);
-        if (ofc == 0) {
-          offset = ll0 ? rep1 : rep0;
-          if (ll0) { rep1 = rep0; rep0 = offset; }
-        } else {
-          const uint32_t idx = 1 + ll0 + zb_read(b, 1);
-          uint32_t t = (idx == 3) ? rep0 - 1 : (idx == 1 ? rep1 : rep2);
-          if (t == 0) return -1;
-          if (idx != 1) rep2 = rep1;
-          rep1 = rep0;
-          rep0 = offset = t;
+    // Sequences are DECODED one after the other (the three FSE states and the repeat offsets form one chain, every lane
+    // computes it: uniform control flow, broadcast table reads) but EXECUTED up to 32 at a time: lane k keeps sequence k
+    // of the pending ones, prefix sums give the literal sources and the output positions, and the copies run lane-parallel
+    // (lz_batch_execute, shared with the LZ4 decoder).  `batch` is off for windows without slack behind `cap` (blocks
+    // decoded straight into the caller's buffer): the lane copies may read a few bytes past a literal run.
+    const MemGeneric W(win);
+    const long litbase = cap - litsize;       // literal k of the block sits at win[litbase + k]
+    long dec = 0;                             // sequences decoded so far
+    int npend = 0;                            // decoded, not yet executed: lanes 0 .. npend - 1
+    const int fill = (batch && nbseq >= 64) ? 32 : 1;   // few sequences are few long matches: one by one, warp-wide
+    int my_ll = 0, my_ml = 0;
+    uint32_t my_off = 0;
+    while (dec < nbseq || npend > 0) {
+      // ---- decode until 32 are pending ------------------------------------------------------------------------------------
+      while (npend < fill && dec < nbseq) {
+        const uint32_t el = z->ll[sl], eo = z->of[so], em = z->ml[sm];
+        const uint32_t llc = el & 0xff, ofc = eo & 0xff, mlc = em & 0xff;
+        if (llc > kZMaxLL || mlc > kZMaxML || ofc > kZMaxOff) return -1;
+        const uint32_t ll_base = kZLLBase[llc];
+        // The fields of a sequence in stream order: offset bits (ofc of them, also for the repeat codes 0 and 1), match
+        // length bits, literal length bits, then the three state updates.  Their widths are all known from the table
+        // entries, so the fields are cut out of ONE 64-bit look at the stream side by side instead of one after the
+        // other through the reader (seven dependent container updates per sequence were most of this loop).
+        const int more = dec + 1 < nbseq;
+        const int n_of = (int)ofc, n_ml = kZMLBits[mlc], n_ll = kZLLBits[llc];
+        const int n_sl = more ? (int)((el >> 8) & 0xff) : 0, n_sm = more ? (int)((em >> 8) & 0xff) : 0,
+                  n_so = more ? (int)((eo >> 8) & 0xff) : 0;
+        const int c1 = n_of, c2 = c1 + n_ml, c3 = c2 + n_ll, c4 = c3 + n_sl, c5 = c4 + n_sm, c6 = c5 + n_so;
+        uint32_t f_of, f_ml, f_ll, f_sl, f_sm, f_so;
+        if (b.avail < 57) zb_refill(b);
+        if (c6 <= b.avail) {
+          const uint64_t c = b.cont;
+          f_of = n_of ? (uint32_t)(c >> (64 - n_of)) : 0u;
+          f_ml = n_ml ? (uint32_t)((c << c1) >> (64 - n_ml)) : 0u;
+          f_ll = n_ll ? (uint32_t)((c << c2) >> (64 - n_ll)) : 0u;
+          f_sl = n_sl ? (uint32_t)((c << c3) >> (64 - n_sl)) : 0u;
+          f_sm = n_sm ? (uint32_t)((c << c4) >> (64 - n_sm)) : 0u;
+          f_so = n_so ? (uint32_t)((c << c5) >> (64 - n_so)) : 0u;
+          b.cont = c6 < 64 ? c << c6 : 0ull;
+          b.avail -= c6;
+          b.bits -= c6;
+        } else {                                  // more than a container's worth (long offsets + long lengths): in turn
+          f_of = zb_read(b, n_of); f_ml = zb_read(b, n_ml); f_ll = zb_read(b, n_ll);
+          f_sl = zb_read(b, n_sl); f_sm = zb_read(b, n_sm); f_so = zb_read(b, n_so);
         }
+        uint32_t offset;
+        if (ofc > 1) {
+          offset = ((1u << ofc) - 3) + f_of;
+          rep2 = rep1; rep1 = rep0; rep0 = offset;
+        } else {
+          const uint32_t ll0 = (ll_base == 0);
+          if (ofc == 0) {
+            offset = ll0 ? rep1 : rep0;
+            if (ll0) { rep1 = rep0; rep0 = offset; }
+          } else {
+            const uint32_t idx = 1 + ll0 + f_of;
+            uint32_t t = (idx == 3) ? rep0 - 1 : (idx == 1 ? rep1 : rep2);
+            if (t == 0) return -1;
+            if (idx != 1) rep2 = rep1;
+            rep1 = rep0;
+            rep0 = offset = t;
+          }
+        }
+        const uint32_t mlen = kZMLBase[mlc] + f_ml;
+        const uint32_t llen = ll_base + f_ll;
+        if (more) {
+          sl = (el >> 16) + f_sl;
+          sm = (em >> 16) + f_sm;
+          so = (eo >> 16) + f_so;
+        }
+        if (b.bits < 0) return -1;
+        if (lane == npend) { my_ll = (int)llen; my_ml = (int)mlen; my_off = offset; }
+        npend++;
+        dec++;
       }
-      const uint32_t mlen = kZMLBase[mlc] + zb_read(b, kZMLBits[mlc]);
-      const uint32_t llen = ll_base + zb_read(b, kZLLBits[llc]);
-      if (i + 1 < nbseq) {
-        sl = (el >> 16) + zb_read(b, (int)((el >> 8) & 0xff));
-        sm = (em >> 16) + zb_read(b, (int)((em >> 8) & 0xff));
-        so = (eo >> 16) + zb_read(b, (int)((eo >> 8) & 0xff));
+      // ---- positions of the pending sequences -------------------------------------------------------------------------------
+      const bool have = lane < npend;
+      const int ll = have ? my_ll : 0, ml = have ? my_ml : 0;
+      const int incl = warp_incl_scan(ll + ml, lane), incl_ll = warp_incl_scan(ll, lane);
+      const long myop = op + incl - ll - ml, cpy = myop + ll, mend = cpy + ml;
+      const long mylit = litpos + incl_ll - ll;            // where this sequence's literals start in the literal buffer
+      // what the one-by-one decoder refuses (zstd_decompress_block.c:896-1010): more literals than the block has, output
+      // beyond the first literal that is still unread after the sequence, an offset beyond the start of the output
+      const bool broken = have && (mylit + ll > litsize || mend > litbase + mylit + ll || (long)my_off > cpy);
+      // lane-parallel copies also need every destination of the batch below the batch's first literal source
+      const bool safe = have && !broken && mend <= litbase + litpos;
+      const unsigned sm_ = __ballot_sync(kFull, safe), bm_ = __ballot_sync(kFull, broken);
+      int cnt = sm_ == kFull ? 32 : __ffs((int)~sm_) - 1;
+      if (bm_ && (int)(__ffs((int)bm_) - 1) <= cnt) return -1;   // the first sequence that cannot run is a broken one
+      if (cnt > 1) {
+        lz_batch_execute(W, W, win, lane, cnt, (int)(litbase + mylit), (int)myop, ll, (int)cpy, (int)my_off, ml);
+      } else {
+        // one sequence the old way (its output may overlap its own literals: z_move_literals reads before it writes)
+        cnt = 1;
+        const int l0 = __shfl_sync(kFull, ll, 0), m0 = __shfl_sync(kFull, ml, 0);
+        const uint32_t o0 = __shfl_sync(kFull, my_off, 0);
+        z_move_literals(win + op, lit + litpos, l0, lane);
+        __syncwarp();
+        lz_match_copy(win, (int)(op + l0), (int)o0, m0, lane);
+        __syncwarp();
       }
-      if (b.bits < 0) return -1;
-      // execute (zstd_decompress_block.c:896-1010)
-      if ((long)llen > litsize - litpos) return -1;
-      // output may grow up to the first literal that is still unread after this sequence
-      if (op + (long)llen + (long)mlen > (cap - litsize) + litpos + (long)llen) return -1;
-      z_move_literals(win + op, lit + litpos, (int)llen, lane);
-      op += llen;
-      litpos += llen;
-      if ((long)offset > op) return -1;
-      __syncwarp();
-      lz_match_copy(win, (int)op, (int)offset, (int)mlen, lane);
-      op += mlen;
+      op = __shfl_sync(kFull, (int)mend, cnt - 1);
+      litpos = __shfl_sync(kFull, (int)(mylit + ll), cnt - 1);
+      my_ll = __shfl_down_sync(kFull, my_ll, (unsigned)cnt);
+      my_ml = __shfl_down_sync(kFull, my_ml, (unsigned)cnt);
+      my_off = __shfl_down_sync(kFull, my_off, (unsigned)cnt);
+      npend -= cnt;
     }
     if (b.bits != 0) return -1;  // must reach the exact start of the bitstream (:1581)
     if (lane == 0) { z->rep[0] = rep0; z->rep[1] = rep1; z->rep[2] = rep2; }
@@ -460,7 +567,9 @@ __device__ __forceinline__ long z_decode_block(ZWork* z, const uint8_t* src, lon
 }
 
 // One or more frames back to back (zstd_decompress.c:447-560, 953-1060).  Returns the decoded size or -1.
-__device__ __forceinline__ long zstd_decode_warp(ZWork* z, const uint8_t* src, long n, uint8_t* dst, long cap) {
+// batch: the window has at least 16 bytes of slack behind dst + cap (see z_decode_block).
+__device__ __forceinline__ long zstd_decode_warp(ZWork* z, const uint8_t* src, long n, uint8_t* dst, long cap,
+                                                 bool batch = false) {
   const int lane = lane_id();
   long ip = 0, total = 0;
   while (ip < n) {
@@ -536,7 +645,7 @@ __device__ __forceinline__ long zstd_decode_warp(ZWork* z, const uint8_t* src, l
         ip += 1;
       } else {
         if (bsize > n - ip || bsize > blockmax) return -1;
-        long r = z_decode_block(z, src + ip, bsize, fdst, op, fcap, blockmax, lane);
+        long r = z_decode_block(z, src + ip, bsize, fdst, op, fcap, blockmax, lane, batch);
         if (r < 0) return -1;
         op = r;
         ip += bsize;
