@@ -157,7 +157,7 @@ struct b2g_ctx {
 namespace {
 
 std::mutex g_attr_mutex;
-size_t g_smem_limit[64][8];  // [device][kernel]
+size_t g_smem_limit[64][12];  // [device][kernel]
 
 int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
   std::lock_guard<std::mutex> lock(g_attr_mutex);
@@ -174,13 +174,15 @@ size_t slab_stride(const b2g_ctx* c);
 // independent worker (window + hash table + encoder work area), so the CTA shape only decides how many fit an SM.
 constexpr int kMaxEncoderStream = 192 * 1024;  // window + 8 KiB table + work area must fit 227 KiB
 struct CompGeom {
-  int win, htab, warps, grid;
+  int win, htab, warps, grid, tile, which;
+  const void* fn;
   size_t smem;
 };
 int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   g.win = std::max((int)align_up((size_t)std::max(max_stream, 1), 16), 1024);
   g.htab = plan_htab_bytes(max_stream);
-  const size_t per = (size_t)g.win + (size_t)g.htab + kEncWorkBytes;
+  g.tile = enc_tile_for(max_stream);
+  const size_t per = (size_t)g.win + (size_t)g.htab + (size_t)enc_work_bytes(g.tile);
   int best = 0;
   g.warps = 1;
   for (int w = 1; w <= 8; w++) {  // k_compress is bounded to 256 threads
@@ -192,9 +194,14 @@ int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   }
   g.smem = (size_t)g.warps * per;
   if (g.smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
-  if (int rc = raise_smem_limit(c->dev, 2, (const void*)k_compress, g.smem)) return rc;
+  // lz4hc chunks hold ordinary LZ4 block streams (format id 1, blosc2.c:2457): the one LZ4 encoder writes both
+  const bool lz4 = c->p.codec == B2G_LZ4 || c->p.codec == B2G_LZ4HC;
+  g.which = (lz4 ? 0 : 2) + (g.tile == 512 ? 0 : 1);
+  g.fn = g.which == 0 ? (const void*)k_compress<kCodecLz4, 512> : g.which == 1 ? (const void*)k_compress<kCodecLz4, 1024>
+       : g.which == 2 ? (const void*)k_compress<kCodecBlosclz, 512> : (const void*)k_compress<kCodecBlosclz, 1024>;
+  if (int rc = raise_smem_limit(c->dev, 8 + g.which, g.fn, g.smem)) return rc;
   int occ = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_compress, 32 * g.warps, g.smem));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, g.fn, 32 * g.warps, g.smem));
   g.grid = c->sms * std::max(occ, 1);
   const size_t max_warps = std::max((size_t)c->sms, ((size_t)1 << 30) / slab_stride(c));
   g.grid = (int)std::min<size_t>((size_t)g.grid, std::max<size_t>(max_warps / g.warps, 1));
@@ -414,9 +421,13 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.n = n;
   ca.win_bytes = g.win;
   ca.htab_bytes = g.htab;
+  ca.tile = g.tile;
   ca.p = cp;
   const int cgrid = (int)std::min<int64_t>(g.grid, (items + g.warps - 1) / g.warps);
-  k_compress<<<cgrid, 32 * g.warps, g.smem, s>>>(ca);
+  {
+    void* kargs[] = {(void*)&ca};
+    CU(cudaLaunchKernel(g.fn, dim3((unsigned)cgrid), dim3((unsigned)(32 * g.warps)), kargs, g.smem, s));
+  }
   c->launches++;
   PlaceArgs pl;
   pl.chunks = ca.chunks;

@@ -287,7 +287,7 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
         else copy_bytes(win + a, payload, csize, lane, 32);
         __syncwarp();
         got = fmt == kFmtLz4 ? lz4_decode_warp_t<true, SMEM>(win + a, csize, win, neblock, a)
-                             : blosclz_decode_warp_t<true>(win + a, csize, win, neblock, a);
+                             : blosclz_decode_batched<true, SMEM>(win + a, csize, win, neblock, a);
       }
     }
     if (got == -2) {  // not staged, or the output caught up with the staged input: decode from the chunk itself
@@ -592,7 +592,8 @@ struct CompressArgs {
   int32_t n;
   int32_t win_bytes;             // shared-memory window of one warp: the largest stream of the batch
   int32_t htab_bytes;            // per-warp hash table bytes (a power of two); each warp's work area is
-                                 // htab_bytes + kEncWorkBytes, see enc_work()
+                                 // htab_bytes + enc_work_bytes(tile), see enc_work()
+  int32_t tile;                  // encoder tile (positions), enc_tile_for(largest stream of the batch)
   CParams p;
 };
 
@@ -669,9 +670,12 @@ __device__ __forceinline__ void gather_plane(int ts, int s, int neblock, const u
 // item: gather + filter into the warp's window, run detection, encode into the item's scratch slot.  Where the stream
 // lands in the chunk depends on the sizes of all earlier streams, so placement is a separate pass (k_place, k_finalize):
 // no warp ever waits for another one.
+// One instantiation per (codec, tile): the encoder is a large loop nest, and a kernel that holds all four variants
+// inline loses 5 % to instruction fetch.
+template <int CODEC, int TILE>
 __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
   const int warp = warp_id(), lane = lane_id();
-  const int wstride = a.win_bytes + a.htab_bytes + kEncWorkBytes;
+  const int wstride = a.win_bytes + a.htab_bytes + enc_work_bytes(TILE);
   uint8_t* win = dyn_smem() + (size_t)warp * (size_t)wstride;   // [win_bytes] the filtered stream
   uint8_t* work = win + a.win_bytes;
   const int ts = a.p.typesize;
@@ -702,13 +706,10 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
       int hlog = 28 - __clz(g.neblock);              // floor(log2(neblock)) - 3: table bytes <= neblock / 4
       const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
       hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
-      const EncWork ew = enc_work(work, a.htab_bytes, hlog);
+      const EncWork ew = enc_work(work, a.htab_bytes, hlog, TILE);
       uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
       const int cap = g.neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
-      int n;
-      // lz4hc chunks hold ordinary LZ4 block streams (format id 1, blosc2.c:2457): the one LZ4 encoder writes both
-      if (a.p.codec == kCodecLz4 || a.p.codec == kCodecLz4hc) n = lz_encode_warp<kCodecLz4>(win, g.neblock, out, cap, ew);
-      else n = lz_encode_warp<kCodecBlosclz>(win, g.neblock, out, cap, ew);
+      const int n = lz_encode_warp<CODEC, TILE>(win, g.neblock, out, cap, ew);
       if (n <= 0 || n >= g.neblock) { r.stored = 1; r.psize = r.csize = g.neblock; }
       else r.psize = r.csize = n;
     }

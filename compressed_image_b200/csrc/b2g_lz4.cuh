@@ -151,7 +151,7 @@ __device__ __forceinline__ void lz_batch_execute(const IN& I, const OUT& O, uint
   for (int i = 0; i < max1; i++)
     if (i < nm1) O.st8(cpy + i, O.ld8(s + i));
   __syncwarp();
-  unsigned rest = __ballot_sync(kFull, exec && !par);
+  unsigned rest = __ballot_sync(kFull, exec && !par && ml > 0);   // (ml == 0: a blosclz literal-run token)
   B2G_SIM_STAT(batches, 1);
   B2G_SIM_STAT(batch_seqs, cnt);
   B2G_SIM_STAT(ordered_matches, __popc(rest));

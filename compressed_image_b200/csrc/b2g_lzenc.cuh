@@ -1,7 +1,7 @@
 // b2g_lzenc.cuh -- tile-phased warp encoder for LZ4 block streams and blosclz streams (rows C1/C3 of SURVEY.md 8a).
 //
 // One warp owns one stream (a byte plane of a shuffled block, resident in shared memory).  The stream is walked in
-// tiles of kEncTile positions, each tile in three phases, so that the only byte-serial part of LZ77 -- the greedy
+// tiles of 512 or 1024 positions, each tile in three phases, so that the only byte-serial part of LZ77 -- the greedy
 // parse -- touches nothing but a few registers and broadcast shared-memory reads:
 //
 //   1. candidates  (position-parallel)  32 positions per step: hash the 4 bytes at p, look the most recent earlier
@@ -24,12 +24,14 @@
 
 namespace b2g {
 
-constexpr int kEncTile = 512;                  // positions per tile = kEncGroups groups of 32 (the flag word of group g
-                                               // lives in lane g): 512 and not 1024 so that ten warps fit an SM
-constexpr int kEncGroups = kEncTile / 32;
-constexpr int kEncMaxSeq = kEncTile / 4;       // every sequence consumes >= 4 positions of its tile
-// per-warp work area after the hash table: off[kEncTile] u16, sp[kEncMaxSeq] u32, sml[kEncMaxSeq] u32, so[kEncMaxSeq] u16
-constexpr int kEncWorkBytes = kEncTile * 2 + kEncMaxSeq * 4 * 2 + kEncMaxSeq * 2;
+// Positions per tile = groups of 32 (the flag word of group g lives in lane g).  Streams above 8 KiB take tiles of 512:
+// their window is what limits the warps per SM, and the smaller work area lets a tenth warp in; smaller streams fit
+// sixteen warps either way and run faster with fewer, larger tiles.
+constexpr int kEncTileMax = 1024;
+__host__ __device__ __forceinline__ int enc_tile_for(int max_stream) { return max_stream > 8192 ? 512 : 1024; }
+// per-warp work area after the hash table: off[tile] u16, sp[tile / 4] u32, sml[tile / 4] u32, so[tile / 4] u16
+// (every sequence consumes >= 4 positions of its tile)
+__host__ __device__ __forceinline__ int enc_work_bytes(int tile) { return tile * 2 + (tile / 4) * 4 * 2 + (tile / 4) * 2; }
 
 #ifdef B2G_SIM
 __device__ __forceinline__ unsigned match_any_u32(unsigned v) { return cusim_match_any(v); }
@@ -39,21 +41,22 @@ __device__ __forceinline__ unsigned match_any_u32(unsigned v) { return __match_a
 
 struct EncWork {
   uint16_t* htab;   // [1 << hlog]
-  uint16_t* off;    // [kEncTile] match distance of a flagged position of the current tile
-  uint32_t* sp;     // [kEncMaxSeq] match start
-  uint32_t* sml;    // [kEncMaxSeq] match length
-  uint16_t* so;     // [kEncMaxSeq] match distance
-  int hlog;
+  uint16_t* off;    // [tile] match distance of a flagged position of the current tile
+  uint32_t* sp;     // [tile / 4] match start
+  uint32_t* sml;    // [tile / 4] match length
+  uint16_t* so;     // [tile / 4] match distance
+  int hlog, tile;
 };
 
-__device__ __forceinline__ EncWork enc_work(uint8_t* base, int htab_bytes, int hlog) {
+__device__ __forceinline__ EncWork enc_work(uint8_t* base, int htab_bytes, int hlog, int tile) {
   EncWork w;
   w.htab = (uint16_t*)base;
   w.off = (uint16_t*)(base + htab_bytes);
-  w.sp = (uint32_t*)(base + htab_bytes + kEncTile * 2);
-  w.sml = w.sp + kEncMaxSeq;
-  w.so = (uint16_t*)(w.sml + kEncMaxSeq);
+  w.sp = (uint32_t*)(base + htab_bytes + tile * 2);
+  w.sml = w.sp + tile / 4;
+  w.so = (uint16_t*)(w.sml + tile / 4);
   w.hlog = hlog;
+  w.tile = tile;
   return w;
 }
 
@@ -71,7 +74,7 @@ constexpr int kEncSelfLit = 16;  // literal runs up to this length are copied by
 // Compresses in[0..n) (shared memory) into out[0..cap) (global or shared).  Returns the compressed size, or 0 when
 // the result does not fit in cap / the stream is too small for the codec (the caller then stores the stream raw, as
 // blosc_c does: blosc2.c:1288-1324).  All 32 lanes call with identical arguments.
-template <int CODEC>
+template <int CODEC, int TILE>
 __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t* out, int cap, const EncWork& w) {
   constexpr bool LZ4 = CODEC == kCodecLz4;
   const int lane = lane_id();
@@ -88,6 +91,7 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
   __syncwarp();
   int anchor = 0, ip = 0, op = 0, step = 1;
   const unsigned lt_mask = (1u << lane) - 1u;
+  constexpr int kEncTile = TILE, kEncGroups = TILE / 32;   // == w.tile (the work area is laid out for it)
   for (int tbase = 0; tbase <= plimit; tbase += kEncTile) {
     if (ip >= tbase + kEncTile) continue;  // the tile lies inside an earlier match
     // ---- phase 1: candidates ----------------------------------------------------------------------------------

@@ -105,8 +105,13 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   ca.items = citems.data(); ca.scratch = scratch.data(); ca.scratch_stride = wwin; ca.n = n;
   const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream);
   ca.win_bytes = wwin; ca.htab_bytes = htab_bytes; ca.p = p;
-  const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + kEncWorkBytes);
-  cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] { k_compress(ca); });
+  ca.tile = enc_tile_for(max_stream);
+  const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));
+  const bool lz4 = codec == kCodecLz4 || codec == kCodecLz4hc;
+  cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] {
+    if (ca.tile == 512) { if (lz4) k_compress<kCodecLz4, 512>(ca); else k_compress<kCodecBlosclz, 512>(ca); }
+    else { if (lz4) k_compress<kCodecLz4, 1024>(ca); else k_compress<kCodecBlosclz, 1024>(ca); }
+  });
   PlaceArgs pl;
   pl.chunks = ch.data(); pl.info = info.data(); pl.items = citems.data(); pl.state = state.data(); pl.n = n;
   cusim::launch(dim3(std::min(grid, n)), dim3(256), 2 * 256 * sizeof(int32_t), [&] { k_place(pl); });
@@ -149,14 +154,20 @@ int sim_stream_decode(int fmt, const void* src, int n, void* dst, int cap) {
 int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int hlog) {
   int result = 0;
   const size_t in_bytes = au((size_t)n + 16, 16);
-  cusim::launch(dim3(1), dim3(32), in_bytes + (2u << hlog) + kEncWorkBytes, [&] {
+  const int tile = enc_tile_for(n);
+  cusim::launch(dim3(1), dim3(32), in_bytes + (2u << hlog) + enc_work_bytes(tile), [&] {
     uint8_t* in = dyn_smem();
     for (int i = (int)threadIdx.x; i < n; i += 32) in[i] = ((const uint8_t*)src)[i];
     __syncwarp();
-    const EncWork ew = enc_work(in + in_bytes, 2 << hlog, hlog);
+    const EncWork ew = enc_work(in + in_bytes, 2 << hlog, hlog, tile);
     int r;
-    if (codec == kCodecLz4) r = lz_encode_warp<kCodecLz4>(in, n, (uint8_t*)dst, cap, ew);
-    else r = lz_encode_warp<kCodecBlosclz>(in, n, (uint8_t*)dst, cap, ew);
+    if (tile == 512) {
+      r = codec == kCodecLz4 ? lz_encode_warp<kCodecLz4, 512>(in, n, (uint8_t*)dst, cap, ew)
+                             : lz_encode_warp<kCodecBlosclz, 512>(in, n, (uint8_t*)dst, cap, ew);
+    } else {
+      r = codec == kCodecLz4 ? lz_encode_warp<kCodecLz4, 1024>(in, n, (uint8_t*)dst, cap, ew)
+                             : lz_encode_warp<kCodecBlosclz, 1024>(in, n, (uint8_t*)dst, cap, ew);
+    }
     if (threadIdx.x == 0) result = r;
   });
   return result;
