@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(HERE, "libb2g.so")
 BLOSCLZ, LZ4, LZ4HC, ZSTD = 0, 1, 2, 5
 NOFILTER, SHUFFLE, BITSHUFFLE = 0, 1, 2
 MAX_OVERHEAD = 32
+NOALLOC_MAX_CHUNKS, NOALLOC_MAX_BLOCKSIZE = 1024, 65536   # b2g.h: limits of b2g_decompress_batch_device_noalloc
 INT32_MAX = 2**31 - 1
 
 
@@ -56,6 +57,8 @@ def lib():
             getattr(L, f).argtypes = [vp, pc, ci, vp]
             getattr(L, f).restype = ci
         L.b2g_wait.argtypes = [vp]
+        L.b2g_decompress_batch_device_noalloc.argtypes = [ci, pc, ci, vp]
+        L.b2g_decompress_batch_device_noalloc.restype = ci
         L.b2g_chunk_sizes.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.b2g_filter_device.argtypes = [vp, ci, ci, ci, ci, vp, vp, C.c_int64, C.c_int32, vp]
         L.b2g_interleave_device.argtypes = [vp, ci, ci, C.POINTER(vp), vp, C.c_int64, vp]
@@ -80,7 +83,7 @@ def lib():
 
 EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
            "b2g_decompress_batch_async", "b2g_compress_batch_device",
-           "b2g_decompress_batch_device", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
+           "b2g_decompress_batch_device", "b2g_decompress_batch_device_noalloc", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
            "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_clone", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 

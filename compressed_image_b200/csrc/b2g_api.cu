@@ -1352,3 +1352,122 @@ int b2g_device_count(void) {
 const char* b2g_version(void) { return "b2g 0.1.0 (sm_100a; blosc2 chunk format 5)"; }
 
 }  // extern "C"
+
+// ---- allocation-free decompress (b2g_decompress_batch_device_noalloc) ---------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture around them, serving loops, harnesses that forbid cudaMalloc): the
+// same plan + decode kernels as b2g_decompress_batch_device, with EVERY work buffer -- chunk descriptors, per-chunk plans,
+// results, item offsets, batch counters, the plane-pairing mailboxes and the ring of staging slots -- carved out of one
+// file-scope device array.  Every GPU that loads the library holds these kNoAllocScratchBytes until the process exits.
+// The array's name is only a host-side stand-in here: the device address comes from cudaGetSymbolAddress, once per device.
+constexpr size_t kNoAllocScratchBytes = (size_t)8 << 20;
+static __device__ __align__(256) uint8_t g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+
+constexpr int kNoAllocSlots = 64;          // staging slots for parked planes (a full ring falls back to the byte scatter)
+constexpr int kNoAllocPairCap = 131072;    // stream items that can take part in plane pairing; later ones scatter
+
+struct NoAllocDev {
+  bool ready = false;
+  uint8_t* scratch = nullptr;              // device address of g_noalloc_scratch on this device
+  DecGeom g{};
+  size_t off_info = 0, off_res = 0, off_base = 0, off_ctl = 0, off_pair = 0, off_stage = 0, slot_bytes = 0;
+};
+NoAllocDev g_noalloc[64];
+std::mutex g_noalloc_mutex;
+
+// Once per device, with that device current.
+int noalloc_setup(int dev, NoAllocDev& D) {
+  if (D.ready) return 0;
+  void* ptr = nullptr;
+  if (cuda_fail(cudaGetSymbolAddress(&ptr, g_noalloc_scratch), "cudaGetSymbolAddress(g_noalloc_scratch)")) return B2G_ERR_NO_DEVICE;
+  if (!ptr) { g_last_error = "cudaGetSymbolAddress returned a null address"; return B2G_ERR_NO_DEVICE; }
+  b2g_ctx tmp;                             // decode_geometry only reads dev, sms and the block sizes
+  tmp.dev = dev;
+  tmp.blocksize = tmp.p.blocksize = B2G_NOALLOC_MAX_BLOCKSIZE;
+  CU(cudaDeviceGetAttribute(&tmp.sms, cudaDevAttrMultiProcessorCount, dev));
+  if (int rc = decode_geometry(&tmp, B2G_NOALLOC_MAX_BLOCKSIZE, false, D.g, true)) return rc;
+  size_t o = 0;
+  o += align_up(sizeof(DChunk) * B2G_NOALLOC_MAX_CHUNKS, 256); D.off_info = o;
+  o += align_up(sizeof(DInfo) * B2G_NOALLOC_MAX_CHUNKS, 256);  D.off_res = o;
+  o += align_up(sizeof(DResult) * B2G_NOALLOC_MAX_CHUNKS, 256); D.off_base = o;
+  o += align_up(sizeof(int32_t) * 2 * (B2G_NOALLOC_MAX_CHUNKS + 1), 256); D.off_ctl = o;
+  o += align_up(sizeof(BatchCtl) * 2, 256); D.off_pair = o;
+  o += align_up(sizeof(int32_t) * ((size_t)kNoAllocSlots + 4 * (size_t)kNoAllocPairCap), 256); D.off_stage = o;
+  D.slot_bytes = align_up((size_t)D.g.wcap, 128);
+  o += D.slot_bytes * kNoAllocSlots;
+  if (o > kNoAllocScratchBytes) { g_last_error = "b2g no-alloc scratch layout exceeds the static array"; return B2G_ERR_FAILURE; }
+  D.scratch = (uint8_t*)ptr;
+  D.ready = true;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2g_decompress_batch_device_noalloc(int device, b2g_chunk* chunks, int n, void* cuda_stream) {
+  if ((!chunks && n > 0) || n < 0) return B2G_ERR_INVALID_PARAM;
+  if (n > B2G_NOALLOC_MAX_CHUNKS) {
+    g_last_error = "b2g_decompress_batch_device_noalloc: " + std::to_string(n) + " chunks in one call, the static scratch holds " +
+                   std::to_string(B2G_NOALLOC_MAX_CHUNKS) + " (B2G_NOALLOC_MAX_CHUNKS); split the batch";
+    return B2G_ERR_MAX_BUFSIZE;
+  }
+  if (n == 0) return 0;
+  if (device < 0) CU(cudaGetDevice(&device));
+  if (device >= 64) return B2G_ERR_INVALID_PARAM;
+  CU(cudaSetDevice(device));
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);   // one call at a time: every call uses the same device array
+  NoAllocDev& D = g_noalloc[device];
+  if (int rc = noalloc_setup(device, D)) return rc;
+  cudaStream_t s = (cudaStream_t)cuda_stream;          // nullptr = the default stream; no stream is created here
+  DChunk h[B2G_NOALLOC_MAX_CHUNKS];                    // host stack, pageable: the copies below stage it before returning
+  DResult r[B2G_NOALLOC_MAX_CHUNKS];
+  for (int i = 0; i < n; i++) {
+    h[i].src = (const uint8_t*)chunks[i].src;
+    h[i].dst = (uint8_t*)chunks[i].dst;
+    h[i].src_bytes = chunks[i].src_bytes;
+    h[i].dst_cap = chunks[i].dst_capacity;
+  }
+  uint8_t* base = D.scratch;
+  const size_t pair_ints = (size_t)kNoAllocSlots + 4 * (size_t)kNoAllocPairCap;
+  // the array keeps the last call's contents: slot flags, mailboxes and block counters must start at zero (the batch
+  // counters, plans, offsets and results are written by k_plan_decode before anything reads them)
+  CU(cudaMemsetAsync(base + D.off_pair, 0, sizeof(int32_t) * pair_ints, s));
+  CU(cudaMemcpyAsync(base, h, sizeof(DChunk) * (size_t)n, cudaMemcpyHostToDevice, s));
+  PlanArgs pa;
+  pa.chunks = (const DChunk*)base;
+  pa.info = (DInfo*)(base + D.off_info);
+  pa.res = (DResult*)(base + D.off_res);
+  pa.base = (int32_t*)(base + D.off_base);
+  pa.ctl = (BatchCtl*)(base + D.off_ctl);
+  pa.n = n;
+  pa.max_block = B2G_NOALLOC_MAX_BLOCKSIZE;            // larger blocks: that chunk fails with B2G_ERR_BLOCKSIZE
+  pa.zstd_ok = 0;                                      // zstd chunks: B2G_ERR_CTX_CODEC (their work area is not in the array)
+  k_plan_decode<<<1, kPlanThreads, kPlanSmemBytes, s>>>(pa);
+  DecodeArgs da;
+  da.chunks = pa.chunks;
+  da.info = pa.info;
+  da.res = pa.res;
+  da.base = pa.base;
+  da.ctl = pa.ctl;
+  da.n = n;
+  da.wcap = D.g.wcap;
+  da.wstride = D.g.wstride;
+  da.slab = nullptr;                                   // every stream of a block <= the maximum fits its shared-memory window
+  da.slab_stride = 0;
+  da.stage = base + D.off_stage;
+  da.slotflag = (int32_t*)(base + D.off_pair);
+  da.mail = da.slotflag + kNoAllocSlots;
+  da.blkcnt = da.mail + 2 * kNoAllocPairCap;
+  da.nslots = kNoAllocSlots;
+  da.slot_bytes = (int32_t)D.slot_bytes;
+  da.pair_cap = kNoAllocPairCap;
+  k_decode<false><<<D.g.grid, 32 * D.g.warps, D.g.smem, s>>>(da);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(r, base + D.off_res, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  for (int i = 0; i < n; i++) {
+    chunks[i].status = r[i].status;
+    chunks[i].out_bytes = r[i].status < 0 ? 0 : r[i].out_bytes;
+  }
+  return 0;
+}

@@ -161,6 +161,23 @@ B2G_API int64_t b2g_launch_count(const b2g_ctx* ctx);
  * kernel: [0] plan/finalize, [1] main codec kernel.  Valid after b2g_wait / a host-pointer batch call. */
 B2G_API int b2g_last_kernel_ms(const b2g_ctx* ctx, float out_ms[2]);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Decompresses n blosc2 chunks
+ * like b2g_decompress_batch_device -- src / dst are DEVICE pointers on `device` (-1 = the current device), codec, filter,
+ * typesize and blocksize come from each chunk's header, out_bytes / status are filled per chunk -- but needs no context and
+ * allocates NOTHING: no cudaMalloc / cudaFree / cudaHostAlloc, no stream or event creation.  All work buffers live in one
+ * static device array of 8 MiB inside the library, which every GPU that loads the library holds until the process exits.
+ * Limits: n <= B2G_NOALLOC_MAX_CHUNKS per call (more: B2G_ERR_MAX_BUFSIZE, b2g_last_error() says why); chunks whose
+ * blocksize exceeds B2G_NOALLOC_MAX_BLOCKSIZE fail individually with B2G_ERR_BLOCKSIZE; lz4 / lz4hc / blosclz / stored /
+ * special-value chunks only (a zstd chunk fails with B2G_ERR_CTX_CODEC).  Synchronous: the work runs on `cuda_stream`
+ * (NULL = the default stream) and the call returns when status / out_bytes are final.  Every call shares the one array,
+ * which keeps the previous call's contents (each call clears what must start at zero).  Calls that overlapped on the GPU
+ * would race on it: the entry point is synchronous and takes a process-wide lock, so calls made through it never do, and
+ * nothing else in the library touches the array. */
+#define B2G_NOALLOC_MAX_CHUNKS 1024
+#define B2G_NOALLOC_MAX_BLOCKSIZE 65536
+B2G_API int b2g_decompress_batch_device_noalloc(int device, b2g_chunk* chunks, int n, void* cuda_stream);
+
 B2G_API const char* b2g_strerror(int code);
 B2G_API const char* b2g_last_error(void); /* thread-local text of the last B2G_ERR_NO_DEVICE-class failure */
 B2G_API int b2g_device_count(void);
