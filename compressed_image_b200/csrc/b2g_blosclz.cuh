@@ -96,6 +96,28 @@ __device__ __forceinline__ int blosclz_decode_batched(const uint8_t* in, int n, 
   for (;;) {
     // ---- parse ahead: nothing but the next token position ------------------------------------------------------------------
     while (!pstop && npend < 32) {
+      // the usual tokens -- literal runs, matches without length extension (near or far) -- with nothing but the next
+      // position on the chain: control byte and the byte after it are loaded together, both candidates for the next
+      // position hang off them side by side, positions are absolute addresses of the view
+      if (pip > 0) {                                            // (the first token carries the marker bit: general path)
+        int base;
+        const auto A = I.origin(base);
+        int pa = base + pip;
+        const int alim = base + nlim;
+        while (npend < 32 && pa < alim) {
+          const uint32_t c = A.ld8(pa), code = A.ld8(pa + 1);
+          const int ql = pa + 2 + (int)c;                       // control byte, c + 1 literals
+          const int qm = pa + ((code == 255u && (c & 31u) == 31u) ? 4 : 2);   // control byte, code [, 16-bit distance]
+          const int q = c < 32u ? ql : qm;
+          if (c >= 224u || q > alim) break;
+          if (lane == npend) tp = pa - base;
+          npend++;
+          pa = q;
+        }
+        pip = pa - base;
+        if (npend == 32) break;
+      }
+      // anything else, one token: the first one, length extensions, the end of the stream
       if (pip >= nlim) { pstop = true; break; }
       uint32_t c = I.ld8(pip);
       if (pip == 0) c &= 31u;
