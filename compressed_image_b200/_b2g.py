@@ -69,6 +69,10 @@ def lib():
         L.b2g_interleave.restype = ci
         L.b2g_deinterleave.restype = ci
         L.b2g_deinterleave_device.restype = ci
+        L.b2g_host_alloc.argtypes = [C.c_size_t]
+        L.b2g_host_alloc.restype = vp
+        L.b2g_host_free.argtypes = [vp]
+        L.b2g_host_free.restype = None
         L.b2g_launch_count.argtypes = [vp]
         L.b2g_launch_count.restype = C.c_int64
         L.b2g_last_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -84,7 +88,7 @@ def lib():
 EXPORTS = ("b2g_create", "b2g_destroy", "b2g_compress_batch", "b2g_decompress_batch", "b2g_compress_batch_async",
            "b2g_decompress_batch_async", "b2g_compress_batch_device",
            "b2g_decompress_batch_device", "b2g_decompress_batch_device_noalloc", "b2g_wait", "b2g_chunk_sizes", "b2g_filter_device", "b2g_interleave_device",
-           "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_clone", "b2g_launch_count",
+           "b2g_deinterleave_device", "b2g_interleave", "b2g_deinterleave", "b2g_host_alloc", "b2g_host_free", "b2g_clone", "b2g_get_params", "b2g_launch_count",
            "b2g_last_kernel_ms", "b2g_strerror", "b2g_last_error", "b2g_device_count", "b2g_version")
 
 

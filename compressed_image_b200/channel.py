@@ -99,6 +99,37 @@ def _pinned_release(buf):
     _pin_free.setdefault(int(buf.nbytes), []).append(buf.reshape(-1).view(np.uint8))
 
 
+def special_value_chunk(value, nbytes, block_size=DEFAULT_BLOCKSIZE):
+    """The chunk blosc2_chunk_zeros / blosc2_chunk_repeatval build (thirdparty/c-blosc2/blosc/blosc2.c:4304-4347,
+    4444-4489) for `nbytes` of one repeated element `value` (a numpy scalar): a 32-byte extended header with
+    blosc2_flags = SPECIAL_ZERO << 4 (all bytes of the value zero) or SPECIAL_VALUE << 4 followed by the value's bytes.
+    Host-side metadata only; decoding it is a fill (blosc2.c:1694-1718; k_decode's special-value items)."""
+    v = np.asarray(value).reshape(1)
+    ts = v.dtype.itemsize
+    nbytes = int(nbytes)
+    if nbytes % ts:
+        raise ValueError("nbytes must be a multiple of the element size")
+    vb = v.view(np.uint8)
+    zero = not vb.any()
+    bs = int(block_size) if int(block_size) > 0 else DEFAULT_BLOCKSIZE     # blosc/stune.c:46-164 with a user blocksize
+    if nbytes < ts:
+        bs = 1
+    else:
+        bs = min(bs, nbytes)
+        if bs > ts:
+            bs = bs // ts * ts
+        bs = max(bs, 1)
+    h = np.zeros(32 + (0 if zero else ts), dtype=np.uint8)
+    h[0], h[1], h[2], h[3] = 5, 1, 0x05, ts                      # format version, blosclz format, extended-header marker
+    h[4:8] = np.frombuffer(np.int32(nbytes).tobytes(), np.uint8)
+    h[8:12] = np.frombuffer(np.int32(bs).tobytes(), np.uint8)
+    h[12:16] = np.frombuffer(np.int32(h.size).tobytes(), np.uint8)
+    h[31] = (1 if zero else 3) << 4                              # BLOSC2_SPECIAL_ZERO / BLOSC2_SPECIAL_VALUE
+    if not zero:
+        h[32:] = vb
+    return h
+
+
 class _Lazy:
     """A lazy fill-value chunk (blosc2/lazyschunk.h:47-105): nbytes of one repeated element, never compressed."""
     __slots__ = ("value", "nbytes")
@@ -250,6 +281,7 @@ class Channel:
     # ---- chunk access ----------------------------------------------------------------------------------------
     def _decode_into(self, indices, outs):
         """Decompress chunks[indices] into the uint8 views `outs` with one batched launch (lazy chunks are fills)."""
+        self._collect_iterators()
         real_c, real_o = [], []
         for i, o in zip(indices, outs):
             c = self._chunks[i]
@@ -289,7 +321,10 @@ class Channel:
             raise ValueError("Invalid chunk size: expected %d elements, got %d" %
                              (self._nbytes_of(i) // self._dtype.itemsize, array.size))
         self._check_encoder()
+        self._collect_iterators()
         self._chunks[i] = self._ctx().compress([array])[0]
+        for _, refresh in getattr(self, "_iter_hooks", ()):
+            refresh(i, array)
 
     def set_chunks(self, chunk_indices, arrays):
         """Batched set_chunk (no reference equivalent: one launch for many chunks)."""
@@ -314,98 +349,157 @@ class Channel:
 
     # ---- chunk iteration (iterators/iterator.h:97-141: decompress -> user modifies -> recompress) --------------
     def __iter__(self):
-        """Yields each chunk as a writable 1-D array; modifications are recompressed when the iterator advances
-        (and at exhaustion), like compressed::channel_iterator.
+        """Yields each chunk as a writable 1-D array; when the iterator advances (and at exhaustion, and when the
+        iteration is abandoned) the chunk is recompressed into the channel, like compressed::channel_iterator, which
+        compresses on every increment whether or not the caller wrote to the span (iterators/iterator.h:97-141, 270-304).
+        A lazy chunk that still holds nothing but its fill value stays lazy.
 
-        Double-buffered: while the caller works on chunk i, chunk i + 1 is already being decompressed and the
-        modified chunk i - 1 is being compressed (b2g_decompress_batch_async / b2g_compress_batch_async on two contexts
-        taken from a free list for the lifetime of the iterator, so that zip() over several channels and get_chunk()
-        calls from inside the loop never meet a context with a batch in flight).  Three buffers rotate: the one the
-        caller holds, the one being filled and the one being read by the compressor."""
+        Pipelined in GROUPS: the chunks are fetched `group` at a time (about 16 MiB, at most 8 chunks) with ONE
+        asynchronous decompress batch, group g + 1 while the caller works on group g; every chunk the caller leaves is
+        handed to one of three compress contexts (b2g_compress_batch_async) and collected later, so the PCIe link carries
+        the next group down and the finished chunks up while the caller computes.  Three group buffers rotate: a view
+        stays valid until the iterator has advanced by two groups.  The contexts come from a free list for the lifetime of
+        the iterator (zip() over several channels and calls on the channel from inside the loop never meet a context with
+        a batch in flight); get_chunk / set_chunk / get_decompressed on the channel first collect what the iterator still
+        has in flight."""
         n = len(self._chunks)
         if n == 0:
             return
         key = (self._codec.blosc2_id, self._level, self._dtype.itemsize, self._filter, self._block_size, self._device)
-        dctx, cctx = _iter_context(key), _iter_context(key)
         itemsize = self._dtype.itemsize
         nb0 = self._nbytes_of(0)
-        bufs = [_pinned(nb0).view(self._dtype) for _ in range(min(n, 3))]
-        before_buf = np.empty(nb0, dtype=np.uint8)                 # reused: no fresh pages per chunk
-        dsts = [_pinned(nb0 + _b2g.MAX_OVERHEAD) for _ in range(2)]
-        fetch = None        # (index, view, batch or None, chunk kept alive)
-        pending = None      # (index, batch, dst, src kept alive)
+        group = max(1, min(8, (16 << 20) // max(nb0, 1), n))
+        ngroups = (n + group - 1) // group
+        ncomp = 3
+        dctx = _iter_context(key)
+        cctxs = [_iter_context(key) for _ in range(min(ncomp, n))]
+        gbufs = [_pinned(nb0 * group) for _ in range(min(ngroups, 3))]
+        dsts = [_pinned(nb0 + _b2g.MAX_OVERHEAD) for _ in cctxs]
+        pending = [None] * len(cctxs)     # per compress context: (index, batch, group buffer index) in flight
+        state = {"fetch": None}
 
-        def start_fetch(i):
-            view = bufs[i % len(bufs)][:self._nbytes_of(i) // itemsize]
-            c = self._chunks[i]
-            if isinstance(c, _Lazy):
-                view[:] = c.value
-                return (i, view, None, None)
-            c = np.ascontiguousarray(c)
-            b = dctx.make_batch([c.ctypes.data], [view.ctypes.data], [int(c.size)], [int(view.nbytes)])
-            dctx.decompress_batch_async(b)
-            return (i, view, b, c)
+        def view_of(i):
+            g, k = divmod(i, group)
+            nb = self._nbytes_of(i)
+            return gbufs[g % len(gbufs)][k * nb0:k * nb0 + nb].view(self._dtype)
 
-        def finish_fetch(f):
-            if f[2] is not None:
+        def collect(slot):
+            p = pending[slot]
+            if p is None:
+                return
+            pending[slot] = None
+            i, b, _gb = p
+            cctxs[slot].wait()
+            if b[0].status < 0:
+                raise _b2g.B2GError(b[0].status, "compress chunk %d" % i)
+            self._chunks[i] = dsts[slot][:b[0].out_bytes].copy()
+
+        def collect_all(gb=None):
+            for slot in range(len(cctxs)):
+                if pending[slot] is not None and (gb is None or pending[slot][2] == gb):
+                    collect(slot)
+
+        def start_fetch(g):
+            gb = g % len(gbufs)
+            collect_all(gb)                 # every compress that still reads this buffer has finished
+            srcs, dsts_, sizes, caps, keep = [], [], [], [], []
+            for i in range(g * group, min(n, (g + 1) * group)):
+                c = self._chunks[i]
+                v = view_of(i)
+                if isinstance(c, _Lazy):
+                    v[:] = c.value
+                    continue
+                c = np.ascontiguousarray(c)
+                keep.append(c)
+                srcs.append(c.ctypes.data)
+                dsts_.append(v.ctypes.data)
+                sizes.append(int(c.size))
+                caps.append(int(v.nbytes))
+            b = None
+            if srcs:
+                b = dctx.make_batch(srcs, dsts_, sizes, caps)
+                dctx.decompress_batch_async(b)
+            state["fetch"] = (g, b, keep)
+            state["hi"] = min(n, (g + 1) * group)
+
+        def finish_fetch():
+            f = state["fetch"]
+            state["fetch"] = None
+            if f is not None and f[1] is not None:
                 dctx.wait()
-                if f[2][0].status < 0:
-                    raise _b2g.B2GError(f[2][0].status, "decompress chunk %d" % f[0])
-            return f[1]
-
-        def collect():
-            nonlocal pending
-            if pending is not None:
-                i, b, dst, _src = pending
-                pending = None
-                cctx.wait()
-                if b[0].status < 0:
-                    raise _b2g.B2GError(b[0].status, "compress chunk %d" % i)
-                self._chunks[i] = dst[:b[0].out_bytes].copy()
+                for k in range(len(f[1])):
+                    if f[1][k].status < 0:
+                        raise _b2g.B2GError(f[1][k].status, "decompress chunk in group %d" % f[0])
 
         def start_compress(i, view):
-            nonlocal pending
-            collect()
+            c = self._chunks[i]
+            if isinstance(c, _Lazy) and bool((view == c.value).all()):
+                return                      # untouched fill: stays lazy
+            slot = i % len(cctxs)
+            collect(slot)
             src = view.view(np.uint8)
-            dst = dsts[i & 1]                                       # the other one may still be held by `pending`
-            b = cctx.make_batch([src.ctypes.data], [dst.ctypes.data], [int(src.size)], [int(dst.size)])
-            cctx.compress_batch_async(b)
-            pending = (i, b, dst, view)
+            dst = dsts[slot]
+            b = cctxs[slot].make_batch([src.ctypes.data], [dst.ctypes.data], [int(src.size)], [int(dst.size)])
+            cctxs[slot].compress_batch_async(b)
+            pending[slot] = (i, b, (i // group) % len(gbufs))
 
+        def refresh(j, array):
+            """set_chunk(j) from inside the loop: a chunk that is already fetched but not yet handed out gets the new data."""
+            if state["cur"] < j < state["hi"]:
+                finish_fetch()
+                view_of(j)[:] = np.asarray(array).reshape(-1)
+
+        state["cur"], state["hi"] = -1, 0
+        hooks = (collect_all, refresh)
+        self._iter_hooks = getattr(self, "_iter_hooks", [])
+        self._iter_hooks.append(hooks)
         try:
-            fetch = start_fetch(0)
-            for i in range(n):
-                buf = finish_fetch(fetch)
-                fetch = None
-                if i + 1 < n:
-                    if len(bufs) < 3 or (pending is not None and pending[0] <= i - 2):
-                        collect()                       # the buffer about to be refilled must have been read
-                    fetch = start_fetch(i + 1)
-                before = before_buf[:buf.nbytes]
-                np.copyto(before, buf.view(np.uint8))
-                try:
-                    yield buf
-                finally:    # also runs when the iteration is abandoned (zip over channels stops at the first
-                    # exhausted iterator): the reference flushes the last chunk in ~channel_iterator (iterator.h:72-93)
-                    if not np.array_equal(before, buf.view(np.uint8)):
+            start_fetch(0)
+            for g in range(ngroups):
+                finish_fetch()
+                if g + 1 < ngroups:
+                    start_fetch(g + 1)
+                for i in range(g * group, min(n, (g + 1) * group)):
+                    state["cur"] = i
+                    buf = view_of(i)
+                    try:
+                        yield buf
+                    finally:    # also runs when the iteration is abandoned (zip over channels stops at the first
+                        # exhausted iterator): the reference flushes the last chunk in ~channel_iterator (iterator.h:72-93)
                         start_compress(i, buf)
         finally:
             try:
-                if fetch is not None:
-                    finish_fetch(fetch)
-                collect()
+                finish_fetch()
+                collect_all()
             finally:
+                self._iter_hooks.remove(hooks)
                 _iter_release(key, dctx)
-                _iter_release(key, cctx)
-                for b in bufs + dsts:
+                for cx in cctxs:
+                    _iter_release(key, cx)
+                for b in gbufs + dsts:
                     _pinned_release(b)
 
-    def chunks(self):
-        """The stored chunk bytes (numpy uint8 arrays; lazy chunks are materialised as blosc2 special chunks)."""
-        out = []
+    def _collect_iterators(self):
+        """Chunks an active iterator is still compressing land in the channel before anything else looks at them."""
+        for flush, _ in getattr(self, "_iter_hooks", ()):
+            flush()
+
+    def chunks(self, special=False):
+        """The stored chunk bytes (numpy uint8 arrays).  Lazy chunks are materialised: by default the fill buffer is
+        compressed, once per distinct (value, size) like lazy_schunk::to_schunk (lazyschunk.h:122-172); with
+        special=True they become blosc2 SPECIAL-VALUE chunks of 32 (+ sizeof(T)) bytes (special_value_chunk below), which
+        any blosc2 decoder expands -- on the GPU that is an O(1)-input fill inside k_decode, the device-resident form of a
+        lazy chunk."""
+        out, cache = [], {}
         for c in self._chunks:
             if isinstance(c, _Lazy):
-                out.append(self._ctx().compress([np.full(c.nbytes // self._dtype.itemsize, c.value, self._dtype)])[0])
+                key = (c.value.tobytes(), c.nbytes)
+                if key not in cache:
+                    if special:
+                        cache[key] = special_value_chunk(c.value, c.nbytes, self._block_size)
+                    else:
+                        cache[key] = self._ctx().compress([np.full(c.nbytes // self._dtype.itemsize, c.value, self._dtype)])[0]
+                out.append(cache[key])
             else:
                 out.append(c)
         return out

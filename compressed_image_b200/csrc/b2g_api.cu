@@ -937,8 +937,12 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
   if (int rc = c->h_desc_all.ensure(sizeof(DChunk) * (size_t)n)) return rc;
   if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
   c->last_ms[0] = c->last_ms[1] = 0;
-  const bool staged = batch_needs_staging(chunks, n);
+  bool staged = batch_needs_staging(chunks, n);
   c->pend_bounds = split_batch(pay, staged);
+  if (staged && c->pend_bounds.size() <= 2) {   // one sub-batch: nothing to overlap, the worker hand-off only adds latency
+    staged = false;
+    c->pend_bounds = split_batch(pay, false);
+  }
   const int nsub = (int)c->pend_bounds.size() - 1;
   if (int rc = ensure_sub_events(c, nsub)) return rc;
   DChunk* desc = (DChunk*)c->h_desc_all.p;
@@ -1075,8 +1079,12 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
   }
   if (int rc = c->d_in.ensure(in_total + 512)) return rc;
   if (int rc = c->d_out.ensure(out_total + 256)) return rc;
-  const bool staged = batch_needs_staging(chunks, n);
+  bool staged = batch_needs_staging(chunks, n);
   c->pend_bounds = split_batch(payload, staged);
+  if (staged && c->pend_bounds.size() <= 2) {
+    staged = false;
+    c->pend_bounds = split_batch(payload, false);
+  }
   const int nsub = (int)c->pend_bounds.size() - 1;
   if (int rc = c->h_desc_all.ensure((sizeof(DChunk) + sizeof(int32_t)) * (size_t)n)) return rc;
   if (int rc = c->h_res_all.ensure(sizeof(DResult) * (size_t)n)) return rc;
@@ -1303,11 +1311,28 @@ int b2g_deinterleave(b2g_ctx* c, int typesize, int nchannels, const void* interl
   return interleave_host(c, false, typesize, nchannels, planes, (void*)interleaved, n_elems);
 }
 
+void* b2g_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cuda_fail(cudaHostAlloc(&p, std::max(bytes, (size_t)1), cudaHostAllocDefault), "cudaHostAlloc")) return nullptr;
+  return p;
+}
+
+void b2g_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
 b2g_ctx* b2g_clone(const b2g_ctx* c) {
   if (!c) return nullptr;
   b2g_params p = c->p;
   p.device = c->dev;
   return b2g_create(&p);
+}
+
+int b2g_get_params(const b2g_ctx* c, b2g_params* out) {
+  if (!c || !out) return B2G_ERR_INVALID_PARAM;
+  *out = c->p;
+  out->device = c->dev;
+  return 0;
 }
 
 int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches.load() : (int64_t)0; }

@@ -180,5 +180,5 @@ def shard_channel(channel, rank, world, group=None):
     nbytes = [channel._nbytes_of(i) for i in range(channel.num_chunks())]
     sc = ShardedChannel(nbytes, rank, world, decode=lambda cs, outs: ctx.decompress(cs, outs),
                         encode=lambda arrs: ctx.compress(arrs), group=group, decode_device=device_decoder(ctx))
-    sc.local_chunks = channel.chunks()[sc.lo:sc.hi]
+    sc.local_chunks = channel.chunks(special=True)[sc.lo:sc.hi]   # lazy chunks travel as 32-byte special-value chunks
     return sc

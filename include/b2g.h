@@ -150,10 +150,21 @@ B2G_API int b2g_interleave(b2g_ctx* ctx, int typesize, int nchannels, const void
 B2G_API int b2g_deinterleave(b2g_ctx* ctx, int typesize, int nchannels, const void* interleaved, void* const* planes,
                              int64_t n_elems);
 
+/* Page-locked (pinned) host memory for buffers that the asynchronous host-pointer calls read or write: only pinned
+ * buffers keep b2g_*_batch_async asynchronous (pageable ones are staged or bounced by the driver).  No reference
+ * counterpart (blosc2 contexts are synchronous); compressed::channel_iterator<T> takes its chunk buffers from here.
+ * b2g_host_alloc returns NULL on failure (b2g_last_error says why). */
+B2G_API void* b2g_host_alloc(size_t bytes);
+B2G_API void b2g_host_free(void* p);
+
 /* A new context with the parameters of `ctx` (its own streams and work buffers): what an iterator takes so that its
  * batches in flight never collide with calls on the channel's own contexts (iterators/iterator.h:209-210 shares them,
  * which is safe there because blosc2 contexts never have work in flight between calls). */
 B2G_API b2g_ctx* b2g_clone(const b2g_ctx* ctx);
+
+/* The parameters `ctx` was created with (device resolved to the ordinal it runs on).  Lets a caller that pools
+ * contexts match a pooled one against the context it would otherwise clone. */
+B2G_API int b2g_get_params(const b2g_ctx* ctx, b2g_params* out);
 
 /* Number of kernels this library has launched through `ctx` since creation (bench.py's gpu_launches). */
 B2G_API int64_t b2g_launch_count(const b2g_ctx* ctx);

@@ -96,6 +96,7 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 		~channel_iterator()
 		{
 			try { flush(); } catch (...) {}  // iterator.h:72-93: the last chunk is written back on scope exit
+			if (m_Pipe && s_Pool.size() < 8) s_Pool.push_back(std::move(m_Pipe));   // contexts + pinned buffers for the next loop
 		}
 
 		value_type operator*()
@@ -118,12 +119,12 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 					wait_fetch();
 					m_Cur = free_buffer(npos);
 					p.buf[m_Cur].resize(m_Schunk->chunk_elements(m_ChunkIndex));
-					m_Schunk->chunk(p.dctx.get(), std::span<T>(p.buf[m_Cur]), m_ChunkIndex);
+					m_Schunk->chunk(p.dctx.get(), p.buf[m_Cur].span(), m_ChunkIndex);
 				}
 				m_Loaded = m_ChunkIndex;
 				start_fetch(m_ChunkIndex + 1);
 			}
-			return value_type(std::span<T>(m_Pipe->buf[m_Cur]), m_Width, m_Height, m_ChunkIndex, m_Schunk->chunk_bytes());
+			return value_type(m_Pipe->buf[m_Cur].span(), m_Width, m_Height, m_ChunkIndex, m_Schunk->chunk_bytes());
 		}
 
 		channel_iterator& operator++()
@@ -146,22 +147,74 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 	private:
 		static constexpr std::size_t npos = static_cast<std::size_t>(-1);
 
+		/// A growable array of page-locked host memory (b2g_host_alloc): what the iterator's batches read and write, so
+		/// that b2g_*_batch_async really returns while the copies run (on pageable memory they are a blocking bounce).
+		template <typename U>
+		struct pinned_array
+		{
+			pinned_array() = default;
+			pinned_array(const pinned_array&) = delete;
+			pinned_array& operator=(const pinned_array&) = delete;
+			~pinned_array() { b2g_host_free(m_Ptr); }
+			void resize(std::size_t count)
+			{
+				if (count > m_Capacity)
+				{
+					b2g_host_free(m_Ptr);
+					m_Ptr = static_cast<U*>(b2g_host_alloc(count * sizeof(U)));
+					m_Capacity = m_Ptr ? count : 0;
+					if (!m_Ptr) throw std::runtime_error(std::string("Unable to allocate pinned host memory: ") + b2g_last_error());
+				}
+				m_Size = count;
+			}
+			U* data() noexcept { return m_Ptr; }
+			std::size_t size() const noexcept { return m_Size; }
+			std::span<U> span() noexcept { return std::span<U>(m_Ptr, m_Size); }
+		private:
+			U* m_Ptr = nullptr;
+			std::size_t m_Size = 0, m_Capacity = 0;
+		};
+
 		/// Everything a batch in flight points at lives here, on the heap, so that moving the iterator moves nothing.
 		struct pipeline
 		{
 			blosc2::context_ptr dctx, cctx;
-			std::vector<T> buf[3];
-			std::vector<std::byte> cbuf;
+			b2g_params key{};                 // parameters of the compress context the pipeline was cloned for
+			pinned_array<T> buf[3];
+			pinned_array<std::byte> cbuf;
 			b2g_chunk fetch_job{}, comp_job{};
 			std::size_t fetch_index = npos, comp_index = npos;
 			std::size_t fetch_buf = 0, comp_buf = 0;
 		};
 
+		/// Pipelines that finished iterators left behind, per thread: creating two contexts (streams, events, device work
+		/// buffers on first use) and four pinned buffers costs tens of milliseconds, a loop over a 64 MiB channel a few.
+		static inline thread_local std::vector<std::unique_ptr<pipeline>> s_Pool;
+
+		static bool same_params(const b2g_params& a, const b2g_params& b) noexcept
+		{
+			return a.codec == b.codec && a.clevel == b.clevel && a.typesize == b.typesize && a.filter == b.filter &&
+				a.blocksize == b.blocksize && a.device == b.device;
+		}
+
 		pipeline& pipe()
 		{
 			if (!m_Pipe)
 			{
+				b2g_params want{};
+				if (b2g_get_params(m_Cctx, &want) == 0)
+				{
+					for (std::size_t k = 0; k < s_Pool.size(); ++k)
+					{
+						if (!same_params(s_Pool[k]->key, want)) continue;
+						m_Pipe = std::move(s_Pool[k]);
+						s_Pool.erase(s_Pool.begin() + static_cast<std::ptrdiff_t>(k));
+						m_Pipe->fetch_index = m_Pipe->comp_index = npos;
+						return *m_Pipe;
+					}
+				}
 				m_Pipe = std::make_unique<pipeline>();
+				m_Pipe->key = want;
 				m_Pipe->dctx = blosc2::context_ptr(b2g_clone(m_Dctx));
 				m_Pipe->cctx = blosc2::context_ptr(b2g_clone(m_Cctx));
 				if (!m_Pipe->dctx || !m_Pipe->cctx)
@@ -236,7 +289,7 @@ namespace NAMESPACE_COMPRESSED_IMAGE
 			const int rc = b2g_wait(p.cctx.get());
 			if (rc < 0 || p.comp_job.status < 0)
 				blosc2::detail::throw_status("Error while compressing blosc2 chunk", rc < 0 ? rc : p.comp_job.status);
-			m_Schunk->set_chunk(std::vector<std::byte>(p.cbuf.begin(), p.cbuf.begin() + p.comp_job.out_bytes), index);
+			m_Schunk->set_chunk(std::vector<std::byte>(p.cbuf.data(), p.cbuf.data() + p.comp_job.out_bytes), index);
 		}
 
 		void flush()

@@ -109,6 +109,19 @@ int ref_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   return run_batch(j, nworkers);
 }
 
+/* blosc2_chunk_zeros / blosc2_chunk_repeatval with the cparams the wrapper builds (blosc2.c:4304-4347, 4444-4489);
+ * repeatval == NULL -> zeros.  -> chunk bytes written, or negative. */
+int ref_special_chunk(int typesize, int blocksize, int32_t nbytes, const void* repeatval, void* dst, int32_t cap) {
+  blosc2_cparams cp = BLOSC2_CPARAMS_DEFAULTS;
+  cp.blocksize = blocksize;
+  cp.typesize = typesize;
+  cp.splitmode = BLOSC_AUTO_SPLIT;
+  cp.clevel = 9;
+  cp.nthreads = 1;
+  cp.compcode = BLOSC_LZ4;
+  return repeatval ? blosc2_chunk_repeatval(cp, nbytes, dst, cap, repeatval) : blosc2_chunk_zeros(cp, nbytes, dst, cap);
+}
+
 /* Raw stream codecs + filters of the reference, for pinning the restatement one layer at a time. */
 extern int LZ4_compress_fast(const char*, char*, int, int, int);
 extern int LZ4_decompress_safe(const char*, char*, int, int);

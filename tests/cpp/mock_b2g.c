@@ -106,6 +106,9 @@ int b2g_deinterleave(b2g_ctx* c, int ts, int nch, const void* inter, void* const
 int b2g_interleave_device(b2g_ctx* c, int ts, int nch, const void* const* p, void* i, int64_t n, void* s) { (void)c; (void)ts; (void)nch; (void)p; (void)i; (void)n; (void)s; return B2G_ERR_NO_DEVICE; }
 int b2g_deinterleave_device(b2g_ctx* c, int ts, int nch, const void* i, void* const* p, int64_t n, void* s) { (void)c; (void)ts; (void)nch; (void)p; (void)i; (void)n; (void)s; return B2G_ERR_NO_DEVICE; }
 int b2g_filter_device(b2g_ctx* c, int f, int fw, int ts, int v, const void* s, void* d, int64_t n, int32_t bs, void* st) { (void)c; (void)f; (void)fw; (void)ts; (void)v; (void)s; (void)d; (void)n; (void)bs; (void)st; return B2G_ERR_NO_DEVICE; }
+int b2g_get_params(const b2g_ctx* c, b2g_params* out) { if (!c || !out) return -12; *out = c->p; return 0; }
+void* b2g_host_alloc(size_t bytes) { return malloc(bytes ? bytes : 1); }
+void b2g_host_free(void* p) { free(p); }
 int64_t b2g_launch_count(const b2g_ctx* c) { return c ? c->launches : 0; }
 int b2g_last_kernel_ms(const b2g_ctx* c, float out[2]) { (void)c; out[0] = out[1] = 0; return 0; }
 const char* b2g_strerror(int code) { (void)code; return "mock"; }

@@ -8,6 +8,7 @@
 //   python/test/test_channel.py:173-237   get_chunk / set_chunk round trip and the exception types
 //   test/src/util.h:40-56                 image_algo::deinterleave as the reference's test helper uses it (+ interleave back)
 // Needs a CUDA device (there is no CPU path); run by tests/test_gpu_cpp.py under -m gpu.
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <numeric>
@@ -319,6 +320,30 @@ static void test_image_batched()
 	CHECK(lazy.num_chunks() == 4 && lazy.is_lazy(3));
 }
 
+// The reference's "modify" usage (benchmark/main.cpp:139-157) on a 64 MiB uint16 channel, timed: iterate, change every
+// value, let the iterator recompress.  Prints the time; checks the data.  Not run against the CPU mock.
+static void bench_iterator_modify()
+{
+	if (std::string(b2g_version()) == "mock") return;
+	const size_t w = 8192, h = 4096;
+	std::vector<uint16_t> data(w * h);
+	uint32_t x = 12345;
+	for (size_t i = 0; i < data.size(); ++i) { x = x * 1664525u + 1013904223u; data[i] = static_cast<uint16_t>(((i % w) >> 2) + ((x >> 28) & 3)); }
+	ci::channel<uint16_t> ch(std::span<const uint16_t>(data), w, h);
+	double best = 1e30;
+	for (int rep = 0; rep < 4; ++rep)
+	{
+		const auto t0 = std::chrono::steady_clock::now();
+		for (auto chunk : ch)
+			for (auto& v : chunk) v ^= 1;
+		const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+		if (rep > 0 && ms < best) best = ms;
+	}
+	std::printf("iterator modify loop, 64 MiB uint16 channel, %zu chunks: %.2f ms (best of 3)\n", ch.num_chunks(), best);
+	const auto back = ch.get_decompressed();       // four passes of ^= 1 cancel out
+	CHECK(back == data);
+}
+
 int main()
 {
 	if (b2g_device_count() < 1)
@@ -345,6 +370,7 @@ int main()
 		test_image<uint8_t>(chunk); test_image<uint16_t>(chunk); test_image<float>(chunk);
 	}
 	test_iterator_pipeline();
+	bench_iterator_modify();
 	test_image_batched();
 	for (size_t nch : { size_t(1), size_t(3), size_t(4), size_t(7), size_t(16) })
 	{

@@ -357,3 +357,36 @@ def test_cfg2_random_access_through_the_api():
             flat[i * per:(i + 1) * per] = new
         out = np.asarray(ch.get_decompressed()).reshape(-1)
         assert np.array_equal(out.view(np.uint16), flat.view(np.uint16))
+
+
+def test_iterator_groups_and_calls_on_the_channel_from_inside_the_loop():
+    """The group-pipelined iterator: a chunk modified in the loop is what get_chunk() returns one step later (the
+    compress in flight is collected first); set_chunk() of a chunk that is already prefetched but not yet handed out is
+    what the iterator then yields; read-only iteration leaves the data alone; 4 MiB chunks (groups of 4)."""
+    import compressed_image_b200 as c
+    w, h = 2048, 10 * 1024 + 100
+    rng = np.random.default_rng(11)
+    data = (np.cumsum(rng.integers(0, 3, size=(h, w)), axis=1) & 0xfff).astype(np.uint16)
+    ch = c.Channel(data, w, h)
+    assert ch.num_chunks() == 11 and ch.chunk_size() == 4 << 20
+    flat = data.reshape(-1).copy()
+    per = ch.chunk_elems()
+    for i, chunk in enumerate(ch):
+        assert np.array_equal(chunk, flat[i * per:i * per + chunk.size]), i
+        chunk ^= 1
+        flat[i * per:i * per + chunk.size] ^= 1
+        if i >= 1:
+            assert np.array_equal(ch.get_chunk(i - 1), flat[(i - 1) * per:i * per]), i
+        if i in (1, 2, 6) and i + 1 < ch.num_chunks():        # next chunk: same group (1, 2, 6 -> 2, 3, 7)
+            new = np.full(ch.chunk_elems(i + 1), 1000 + i, np.uint16)
+            ch.set_chunk(i + 1, new)
+            flat[(i + 1) * per:(i + 1) * per + new.size] = new
+    assert np.array_equal(np.asarray(ch.get_decompressed()).reshape(-1), flat)
+    total = 0
+    for chunk in ch:                                          # read-only
+        total += int(chunk[0])
+    assert np.array_equal(np.asarray(ch.get_decompressed()).reshape(-1), flat)
+    lazy = c.Channel.zeros(np.float32, 1024, 4096)
+    for chunk in lazy:
+        assert not chunk.any()
+    assert lazy.compressed_bytes() == 4 * lazy.num_chunks()   # still lazy: sizeof(T) per chunk (lazyschunk.h:312-327)
