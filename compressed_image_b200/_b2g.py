@@ -220,15 +220,24 @@ class Context:
         """list of numpy arrays (raw elements) -> list of chunks (numpy uint8), one batched launch."""
         import numpy as np
         srcs = [np.ascontiguousarray(a).reshape(-1).view(np.uint8) for a in arrays]
-        dsts = [np.empty(s.size + MAX_OVERHEAD, dtype=np.uint8) for s in srcs]
-        b = self.make_batch([s.ctypes.data for s in srcs], [d.ctypes.data for d in dsts], [int(s.size) for s in srcs],
-                            [int(d.size) for d in dsts])
+        # worst-case destinations come out of one arena the context keeps (fresh 4 MiB buffers per chunk would be page
+        # faults on every call); the chunks are copied out at their compressed size
+        offs, total = [], 0
+        for s in srcs:
+            offs.append(total)
+            total += (int(s.size) + MAX_OVERHEAD + 63) // 64 * 64
+        arena = getattr(self, "_arena", None)
+        if arena is None or arena.size < total:
+            arena = self._arena = np.empty(max(total, 1 << 20), dtype=np.uint8)
+        base = arena.ctypes.data
+        b = self.make_batch([s.ctypes.data for s in srcs], [base + o for o in offs], [int(s.size) for s in srcs],
+                            [int(s.size) + MAX_OVERHEAD for s in srcs])
         self.compress_batch(b)
         out = []
-        for i, d in enumerate(dsts):
+        for i, o in enumerate(offs):
             if b[i].status < 0:
                 raise B2GError(b[i].status, "compress chunk %d" % i)
-            out.append(d[:b[i].out_bytes].copy())
+            out.append(arena[o:o + b[i].out_bytes].copy())
         return out
 
     def decompress(self, chunks, outs=None, trust_header=False):

@@ -751,6 +751,11 @@ static std::vector<int> split_batch(const std::vector<size_t>& payload, bool sta
 // the copy of the per-chunk results, on the lane streams in rotation.  Decompress also enqueues its D2H copies (the sizes
 // are in the headers); compress copies a chunk back once its size is known, from b2g_wait(), on a stream of its own so
 // that those copies never queue behind the H2D copies of later sub-batches.
+static void drain_lanes(b2g_ctx* c) {
+  for (Lane& L : c->lanes) if (L.stream) cudaStreamSynchronize(L.stream);
+  if (c->d2h_stream) cudaStreamSynchronize(c->d2h_stream);
+}
+
 static int ensure_sub_events(b2g_ctx* c, int nsub) {
   while ((int)c->sub_done.size() < nsub) {
     cudaEvent_t e = nullptr;
@@ -1015,6 +1020,9 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
     c->pend = chunks; c->pend_n = n; c->pend_kind = 3;
     return 0;
   }
+  // An error after the first enqueue must not leave copies and kernels in flight on the caller's buffers and the staging
+  // areas: the whole loop runs in a lambda, and a failure drains every lane before it is reported.
+  auto enqueue_all = [&]() -> int {
   for (int k = 0; k < nsub; k++) {
     Lane& L = c->lanes[k % g_lanes];
     const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
@@ -1044,6 +1052,9 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
     }
     CU(cudaEventRecord(c->sub_done[k], s));
   }
+  return 0;
+  };
+  if (int rc = enqueue_all()) { drain_lanes(c); return rc; }
   c->pend = chunks; c->pend_n = n; c->pend_kind = 1;
   return 0;
 }
@@ -1163,6 +1174,9 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
     c->pend = chunks; c->pend_n = n; c->pend_kind = 3;
     return 0;
   }
+  // An error after the first enqueue must not leave copies and kernels in flight on the caller's buffers and the staging
+  // areas: the whole loop runs in a lambda, and a failure drains every lane before it is reported.
+  auto enqueue_all = [&]() -> int {
   for (int k = 0; k < nsub; k++) {
     Lane& L = c->lanes[k % g_lanes];
     const int lo = c->pend_bounds[k], cnt = c->pend_bounds[k + 1] - lo;
@@ -1191,6 +1205,9 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
     if (int rc = enqueue_compress(c, L, desc + lo, nb + lo, cnt, s, ci + lo, base + lo + k, res + lo)) return rc;
     CU(cudaEventRecord(c->sub_done[k], s));
   }
+  return 0;
+  };
+  if (int rc = enqueue_all()) { drain_lanes(c); return rc; }
   c->pend = chunks; c->pend_n = n; c->pend_kind = 2;
   return 0;
 }

@@ -139,3 +139,62 @@ def test_cfg5_chunk_size_sweep(chunk_kib, codec, filt):
         assert len(pieces) == (32 << 20) // (chunk_kib * 1024)
         ratio, _ = _device_round_trip(pieces, codec, 9, ts, filt, ref_sample=2)
         assert ratio > 1.0
+
+
+# ---- full configured sizes through the HOST path (split_batch, address-ordered merging, staging threads) ----------------
+def _host_round_trip_full(pieces, codec, typesize, filt, views=None):
+    """One host-pointer compress batch over ALL chunks of the configuration, one host-pointer decompress batch of the
+    results into ONE output array (neighbouring outputs: merged copies), pageable numpy memory (the staged path).  Checks:
+    every status 0, the output equals the inputs chunk by chunk, the reference decodes a sample of the GPU chunks."""
+    from compressed_image_b200 import _b2g
+    n = len(pieces)
+    with _b2g.Context(codec, 9, typesize, filt, BLOCK) as ctx:
+        launches0 = ctx.launches
+        chunks = ctx.compress(pieces)
+        assert len(chunks) == n
+        sizes = [int(p.size) for p in pieces]
+        out = np.empty(sum(sizes), np.uint8)
+        outs, o = [], 0
+        for s in sizes:
+            outs.append(out[o:o + s])
+            o += s
+        order = np.random.default_rng(7).permutation(n)             # the batch in scrambled order: sorted by address inside
+        res = ctx.decompress([chunks[i] for i in order], [outs[i] for i in order])
+        assert len(res) == n
+        # a few hundred chunks per launch, not one launch per chunk: 1536 chunks of 4 MiB are ~200 sub-batches of 32 MiB
+        assert ctx.launches - launches0 <= 12 * (sum(sizes) // (8 << 20) + 2)
+    o = 0
+    for i, p in enumerate(pieces):
+        assert np.array_equal(out[o:o + sizes[i]], np.ascontiguousarray(p).reshape(-1).view(np.uint8)), i
+        o += sizes[i]
+    for i in np.linspace(0, n - 1, num=6, dtype=int):
+        rc, back = (_libs.ref_decompress if HAVE_REF else _libs.oracle_decompress)(chunks[i])
+        assert rc == sizes[i] and np.array_equal(back, np.ascontiguousarray(pieces[i]).reshape(-1).view(np.uint8)), i
+    return sum(sizes) / sum(int(c.size) for c in chunks)
+
+
+def test_cfg3_full_size_host_path():
+    """cfg 3 at its configured size: 16 float channels of 8192 x 8192 = 1024 chunks, 4 GiB, blosclz + bitshuffle, one batch
+    (four synthetic channels, one per kind, each standing for four channels of the stack)."""
+    from compressed_image_b200 import _b2g, synth
+    pieces = []
+    for k, kind in enumerate(synth.F32_KINDS):
+        chan = synth.split_chunks(synth.f32_channel(8192, 8192, kind, channel=k), CHUNK)
+        pieces += chan * 4
+    assert len(pieces) == 1024
+    ratio = _host_round_trip_full(pieces, _b2g.BLOSCLZ, 4, _b2g.BITSHUFFLE)
+    assert 2.0 < ratio < 5.0
+
+
+def test_cfg4_full_size_host_path():
+    """cfg 4 at its configured size: 256 uint16 RGB images of 2048 x 2048 = 1536 chunks, 6 GiB, lz4 + shuffle, one batch
+    (32 distinct synthetic images, each standing for eight images of the batch)."""
+    from compressed_image_b200 import _b2g, synth
+    pieces = []
+    for im in range(32):
+        for ch in range(3):
+            pieces += synth.split_chunks(synth.u16_sensor_channel(2048, 2048, ch, image=im), CHUNK)
+    pieces = pieces * 8
+    assert len(pieces) == 1536
+    ratio = _host_round_trip_full(pieces, _b2g.LZ4, 2, _b2g.SHUFFLE)
+    assert 1.5 < ratio < 2.5
