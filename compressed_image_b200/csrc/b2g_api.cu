@@ -180,7 +180,7 @@ struct CompGeom {
 };
 int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   g.win = std::max((int)align_up((size_t)std::max(max_stream, 1), 16), 1024);
-  g.htab = plan_htab_bytes(max_stream);
+  g.htab = plan_htab_bytes(max_stream, c->p.clevel);
   g.tile = enc_tile_for(max_stream);
   const size_t per = (size_t)g.win + (size_t)g.htab + (size_t)enc_work_bytes(g.tile);
   int best = 0;

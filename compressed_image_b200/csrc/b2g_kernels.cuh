@@ -706,11 +706,15 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
       int hlog = 28 - __clz(g.neblock);              // floor(log2(neblock)) - 3: table bytes <= neblock / 4
       const int hmax = 30 - __clz(a.htab_bytes);     // log2(htab_bytes / 2)
       hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
-      const EncWork ew = enc_work(work, a.htab_bytes, hlog, TILE);
+      const EncWork ew = enc_work(work, a.htab_bytes, hlog, TILE, CODEC == kCodecBlosclz || a.p.clevel > 5 ? 4 : (a.p.clevel > 2 ? 5 : 6));   // == plan_min_match (b2g_plan.h is host code)
       uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
       const int cap = g.neblock - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
       const int n = lz_encode_warp<CODEC, TILE>(win, g.neblock, out, cap, ew);
-      if (n <= 0 || n >= g.neblock) { r.stored = 1; r.psize = r.csize = g.neblock; }
+      // below level 9 a stream that the codec shrinks by next to nothing is stored (like the reference's blosclz, which
+      // gives up on a block whose estimated ratio is under 1.0 .. 1.2 depending on the level, blosclz.c:463-468): the
+      // bytes saved are within 0.8 % / 1.6 % / 3 % of the stream, and a stored stream decodes as a copy
+      const int margin = a.p.clevel >= 9 ? 0 : (a.p.clevel >= 6 ? g.neblock >> 7 : (a.p.clevel >= 3 ? g.neblock >> 6 : g.neblock >> 5));
+      if (n <= 0 || n >= g.neblock - margin) { r.stored = 1; r.psize = r.csize = g.neblock; }
       else r.psize = r.csize = n;
     }
     if (lane == 0) a.items[item] = r;

@@ -46,9 +46,10 @@ struct EncWork {
   uint32_t* sml;    // [tile / 4] match length
   uint16_t* so;     // [tile / 4] match distance
   int hlog, tile;
+  int minml;        // shortest match worth a sequence (4 = every match the format allows)
 };
 
-__device__ __forceinline__ EncWork enc_work(uint8_t* base, int htab_bytes, int hlog, int tile) {
+__device__ __forceinline__ EncWork enc_work(uint8_t* base, int htab_bytes, int hlog, int tile, int minml = 4) {
   EncWork w;
   w.htab = (uint16_t*)base;
   w.off = (uint16_t*)(base + htab_bytes);
@@ -57,6 +58,7 @@ __device__ __forceinline__ EncWork enc_work(uint8_t* base, int htab_bytes, int h
   w.so = (uint16_t*)(w.sml + tile / 4);
   w.hlog = hlog;
   w.tile = tile;
+  w.minml = minml;
   return w;
 }
 
@@ -204,6 +206,12 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         }
       }
       if (!LZ4 && dist - 1 >= kBlzMaxDistance && ml < 8) {  // a 4-byte far token does not pay for a short match
+        ip = p + 1;
+        continue;
+      }
+      // the faster levels leave the matches that save a byte or less in the literals (a 4-byte LZ4 match costs a token and
+      // an offset: noisy byte planes are full of them, and every one is a sequence for the decoder)
+      if (ml < w.minml && !(can_back && pb == cb)) {
         ip = p + 1;
         continue;
       }

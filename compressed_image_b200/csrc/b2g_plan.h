@@ -57,12 +57,24 @@ inline int plan_nstreams(int codec, int clevel, int filter, int typesize, int bl
 }
 inline int plan_cta_warps(int nstreams) { return std::min(std::max(nstreams, 1), kCtaWarps); }
 
+// Effort by compression level.  The reference's LZ4 path ignores clevel (accel is forced to 1, blosc2.c:413) and its
+// blosclz path sizes the hash table by it (blosclz.c:57-62, 442-444); here clevel 9 -- what compressed-image uses by
+// default -- means every match the format allows through the largest table, and the lower levels trade ratio for speed
+// on both sides of the codec: a smaller table (one more warp per SM, fewer candidates to verify) and, for LZ4 from level
+// 5 down, no sequences for matches that save a byte or less (two bytes or less at levels 1 and 2).
+inline int plan_htab_shrink(int clevel) { return clevel >= 9 ? 0 : (clevel >= 6 ? 1 : 2); }
+inline int plan_min_match(int codec, int clevel) {
+  if (codec == kCodecBlosclz || clevel > 5) return 4;
+  return clevel > 2 ? 5 : 6;
+}
+
 // Per-warp hash table of the encoder for streams of `neblock` bytes: 2^hlog uint16 entries with
-// hlog = floor(log2(neblock)) - 3 clamped to [6, 12] (table bytes <= neblock / 4; k_compress derives the same hlog).
-inline int plan_htab_bytes(int neblock) {
+// hlog = floor(log2(neblock)) - 3 - shrink clamped to [6, 12] (table bytes <= neblock / 4; k_compress derives the same
+// hlog from the table size it is given).
+inline int plan_htab_bytes(int neblock, int clevel = 9) {
   int lg = 0;
   while ((2 << lg) <= std::max(neblock, 1)) lg++;   // floor(log2(neblock))
-  const int hlog = std::min(std::max(lg - 3, 6), 12);
+  const int hlog = std::min(std::max(lg - 3 - plan_htab_shrink(clevel), 6), 12);
   return 2 << hlog;
 }
 

@@ -103,7 +103,7 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   CompressArgs ca;
   ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
   ca.items = citems.data(); ca.scratch = scratch.data(); ca.scratch_stride = wwin; ca.n = n;
-  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream);
+  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);
   ca.win_bytes = wwin; ca.htab_bytes = htab_bytes; ca.p = p;
   ca.tile = enc_tile_for(max_stream);
   const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));

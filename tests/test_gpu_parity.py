@@ -313,3 +313,29 @@ def test_damaged_payloads_same_decisions_as_reference():
             assert (st < 0) == (rc < 0), (st, rc)
             if rc >= 0:
                 assert np.array_equal(out, exp)
+
+
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+@pytest.mark.parametrize("ts", [1, 2, 4])
+def test_every_compression_level_is_reference_decodable(codec, ts):
+    """The encoder's effort follows clevel (b2g_plan.h: table size, shortest match worth a sequence, the margin under which
+    a stream is stored): whatever the level, the reference decodes every chunk bit-exactly, the GPU does too, and level 9
+    compresses at least as well as the faster levels (to within a few bytes of framing)."""
+    g = _gpu()
+    srcs = [_data.make_data(k, 400000 + ts * i, ts, seed=i) for i, k in enumerate(("half", "sensor", "text", "ramp", "f32", "random"))]
+    sizes = {}
+    for clevel in (1, 2, 3, 5, 6, 8, 9):
+        res = g.compress_batch(srcs, codec, clevel, ts, _data.SHUFFLE, 32768)
+        total = 0
+        for (st, chunk), src in zip(res, srcs):
+            assert st == 0
+            raw = src.reshape(-1).view(np.uint8)
+            rc, back = _checker_decompress(chunk)
+            assert rc == raw.size and np.array_equal(back, raw), (clevel, ts)
+            total += chunk.size
+        outs = g.decompress_batch([c for _, c in res])
+        for (st, out), src in zip(outs, srcs):
+            assert st == 0 and np.array_equal(out, src.reshape(-1).view(np.uint8))
+        sizes[clevel] = total
+    assert sizes[9] <= min(sizes.values()) * 1.002
+    assert sizes[1] <= sizes[9] * 1.12          # the fast levels give up a few per cent, not the compression
