@@ -228,7 +228,7 @@ size_t slab_stride(const b2g_ctx* c) {
 // Decode launch geometry for streams of `stream_bytes`: every warp is an independent worker with its own window, so
 // the CTA shape only matters for how many warps fit an SM's shared memory (228 KiB, 1 KiB reserved per CTA).
 struct DecGeom {
-  int wcap, wstride, warps, grid;
+  int wcap, wstride, warps, grid, bulk;
   size_t smem;
 };
 // lz4 / blosclz streams are decoded in place in batches of up to 32 sequences, and a batch may only produce as many bytes
@@ -260,6 +260,9 @@ int decode_geometry(b2g_ctx* c, int stream_bytes, bool zstd, DecGeom& g, bool an
     g.wstride = g.wcap;
   }
   g.smem = (size_t)g.warps * g.wstride;
+  static const bool bulk_on = [] { const char* e = getenv("B2G_BULK_STAGE"); return !(e && e[0] == '0'); }();
+  g.bulk = (!zstd && bulk_on && g.smem + 8 * (size_t)g.warps <= 227 * 1024) ? 1 : 0;   // one mbarrier per warp behind the windows
+  if (g.bulk) g.smem += 8 * (size_t)g.warps;
   const void* fn = zstd ? (const void*)k_decode<true> : (const void*)k_decode<false>;
   if (int rc = raise_smem_limit(c->dev, zstd ? 1 : 0, fn, g.smem)) return rc;
   int occ = 0;
@@ -340,6 +343,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
   da.nslots = nslots;
   da.slot_bytes = (int32_t)slot_bytes;
   da.pair_cap = (int32_t)pair_cap;
+  da.bulk = g.bulk;
   k_decode<false><<<g.grid, 32 * g.warps, g.smem, s>>>(da);
   c->launches++;
   if (want_zstd) {
@@ -347,6 +351,7 @@ int enqueue_decode(b2g_ctx* c, Lane& L, const DChunk* h_desc, int n, cudaStream_
     da.ctl = pa.ctl + 1;
     da.wcap = gz.wcap;
     da.wstride = gz.wstride;
+    da.bulk = 0;
     da.mail += pair_cap;     // the zstd class numbers its items from 0 again
     da.blkcnt += pair_cap;
     k_decode<true><<<gz.grid, 32 * gz.warps, gz.smem, s>>>(da);
@@ -1503,6 +1508,7 @@ extern "C" int b2g_decompress_batch_device_noalloc(int device, b2g_chunk* chunks
   da.nslots = kNoAllocSlots;
   da.slot_bytes = (int32_t)D.slot_bytes;
   da.pair_cap = kNoAllocPairCap;
+  da.bulk = D.g.bulk;
   k_decode<false><<<D.g.grid, 32 * D.g.warps, D.g.smem, s>>>(da);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(r, base + D.off_res, sizeof(DResult) * (size_t)n, cudaMemcpyDeviceToHost, s));

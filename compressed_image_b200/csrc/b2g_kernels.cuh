@@ -210,6 +210,7 @@ struct DecodeArgs {
   int32_t* mail;         // [pair_cap] per item: 0 nothing yet, slot + 1 = parked there, -1 = scattered directly
   int32_t* blkcnt;       // [pair_cap] per block (index = its first item): planes finished
   int32_t nslots, slot_bytes, pair_cap;
+  int32_t bulk;          // 1: 8 bytes per warp behind the windows hold the mbarriers of the bulk payload staging
 };
 
 // Window bytes needed to decode a stream of `neblock` bytes with its compressed bytes staged in place above the output.
@@ -247,12 +248,48 @@ __device__ __forceinline__ void stage_payload(uint8_t* dst, const uint8_t* src, 
   async_copy_wait();
 }
 
+// The same staging with the aligned body moved by ONE bulk copy of the async proxy (cp.async.bulk, the 1-D form of TMA: no
+// tensor map) instead of n / 16 per-lane copies: lane 0 posts the byte count on the warp's mbarrier and issues the copy,
+// the lanes bring in the unaligned head and tail, everybody waits on the barrier's phase.  `bar` lives in shared memory
+// (initialised with count 1 at kernel start), `phase` is the warp's running parity.
+struct StageBar {
+  uint64_t* bar;
+  uint32_t phase;
+};
+
+#ifndef B2G_SIM
+__device__ __forceinline__ void stage_payload_bulk(uint8_t* dst, const uint8_t* src, int n, int lane, StageBar& sb) {
+  int head = (int)((16 - ((uintptr_t)src & 15)) & 15);
+  if (head > n) head = n;
+  const int body = (n - head) & ~15;
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(sb.bar);
+  if (body > 0 && lane == 0) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + head);
+    // the window was written through the generic proxy (the previous stream's output): order that before the async write
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)body) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(d), "l"(src + head), "r"((uint32_t)body), "r"(bar) : "memory");
+  }
+  if (lane < head) dst[lane] = src[lane];
+  for (int i = head + body + lane; i < n; i += 32) dst[i] = src[i];
+  if (body > 0) {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(bar), "r"(sb.phase) : "memory");
+    }
+    sb.phase ^= 1u;
+  }
+}
+#endif
+
 // One stream (blosc2.c:1783-1923) decoded by one warp into win[0..neblock).  `wbytes` = usable bytes of the window:
 // lz4 / blosclz streams are first copied to its top (16-byte loads, same alignment phase as the source) and decoded in
 // place, so the byte-serial part of the decoder only ever touches the window.
 template <bool Z, bool STAGE, bool SMEM>
 __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, int32_t csize, int32_t avail,
-                                             uint8_t* win, int32_t wbytes, int32_t neblock, ZWork* zw) {
+                                             uint8_t* win, int32_t wbytes, int32_t neblock, ZWork* zw, StageBar* sb) {
   const int lane = lane_id();
   if (csize == 0) {
     fill_bytes(win, 0, neblock, lane, 32);
@@ -283,8 +320,15 @@ __device__ __forceinline__ int decode_stream(int fmt, const uint8_t* payload, in
       const int m = (int)((uintptr_t)payload & 15);
       const int a = ((wbytes - csize - m) & ~15) + m;  // a + csize <= wbytes, (win + a) = payload (mod 16)
       if (wbytes - csize - m >= 0) {
-        if (SMEM) stage_payload(win + a, payload, csize, lane);  // asynchronous 16-byte copies, all in flight at once
-        else copy_bytes(win + a, payload, csize, lane, 32);
+        if (SMEM) {
+#ifndef B2G_SIM
+          if (sb) stage_payload_bulk(win + a, payload, csize, lane, *sb);   // one bulk copy (async proxy) + head / tail
+          else
+#endif
+            stage_payload(win + a, payload, csize, lane);  // asynchronous 16-byte copies, all in flight at once
+        } else {
+          copy_bytes(win + a, payload, csize, lane, 32);
+        }
         __syncwarp();
         got = fmt == kFmtLz4 ? lz4_decode_warp_t<true, SMEM>(win + a, csize, win, neblock, a)
                              : blosclz_decode_batched<true, SMEM>(win + a, csize, win, neblock, a);
@@ -473,7 +517,7 @@ __device__ __forceinline__ void unfilter_streams(const DecodeArgs& a, const Stre
 
 template <bool Z, bool STAGE, bool SMEM>
 __device__ __forceinline__ int decode_streams(const DecodeArgs& a, const StreamJob& jb, uint8_t* win, int32_t wbytes,
-                                              ZWork* zw) {
+                                              ZWork* zw, StageBar* sb) {
   // stream directory: each csize tells where the next stream starts (warp-uniform loads)
   int32_t pos = jb.first;
   if (pos <= 0 || pos >= jb.srcsize) return kErrData;
@@ -487,7 +531,7 @@ __device__ __forceinline__ int decode_streams(const DecodeArgs& a, const StreamJ
     if (k >= jb.s) {
       const int32_t o = jb.scatter ? 0 : k * jb.neblock;  // a plane has the window to itself
       const int rc = decode_stream<Z, STAGE, SMEM>(jb.fmt, jb.src + pos, cs, jb.srcsize - pos, win + o, wbytes - o,
-                                             jb.neblock, zw);
+                                             jb.neblock, zw, sb);
       if (rc < 0) return rc;
     }
     pos += cs > 0 ? cs : (cs < 0 ? 1 : 0);
@@ -503,6 +547,21 @@ __global__ void __launch_bounds__(512, 1) k_decode(DecodeArgs a) {
   uint8_t* win_s = dyn_smem() + (size_t)warp * (size_t)a.wstride;
   ZWork* zw = Z ? (ZWork*)(win_s + a.wcap) : nullptr;
   const int gwarp = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp;
+  // payload staging by bulk copy: one mbarrier per warp behind the windows (a.bulk: the launch reserved the room)
+  StageBar sbar{nullptr, 0};
+  StageBar* sb = nullptr;
+  (void)sbar;
+#ifndef B2G_SIM
+  if (!Z && a.bulk) {
+    sbar.bar = (uint64_t*)(dyn_smem() + (size_t)(blockDim.x >> 5) * (size_t)a.wstride) + warp;
+    if (lane == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(sbar.bar)) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    sb = &sbar;
+  }
+#endif
   int hint = 0;
   for (;;) {
     int item = 0;
@@ -550,9 +609,9 @@ __global__ void __launch_bounds__(512, 1) k_decode(DecodeArgs a) {
     jb.s = g.s; jb.s_end = g.s_end; jb.ns = g.ns; jb.neblock = neblock; jb.bsize = bsize; jb.scatter = g.scatter;
     jb.fmt = d.fmt; jb.filter = d.filter; jb.typesize = d.typesize; jb.version = d.version; jb.item = item;
     int err;
-    if (need <= a.wcap) err = decode_streams<Z, true, true>(a, jb, win_s, a.wcap, zw);
-    else if (direct) err = decode_streams<Z, false, false>(a, jb, raw, bsize, zw);
-    else err = decode_streams<Z, true, false>(a, jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw);
+    if (need <= a.wcap) err = decode_streams<Z, true, true>(a, jb, win_s, a.wcap, zw, sb);
+    else if (direct) err = decode_streams<Z, false, false>(a, jb, raw, bsize, zw, nullptr);
+    else err = decode_streams<Z, true, false>(a, jb, a.slab + (size_t)gwarp * (size_t)a.slab_stride, need, zw, nullptr);
     if (err && lane == 0) set_status(a.res, c, err);
     __syncwarp();  // the window is free for the next item
   }

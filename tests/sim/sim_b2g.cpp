@@ -50,7 +50,7 @@ int sim_decompress_batch(int n, const void* const* srcs, const int32_t* srcsizes
   std::vector<int32_t> pairmeta(nslots + 4 * pair_cap + 4, 0);
   da.stage = pair ? stage.data() : nullptr;
   da.slotflag = pairmeta.data(); da.mail = da.slotflag + nslots; da.blkcnt = da.mail + 2 * pair_cap;
-  da.nslots = nslots; da.slot_bytes = win_bytes; da.pair_cap = (int32_t)pair_cap;
+  da.nslots = nslots; da.slot_bytes = win_bytes; da.pair_cap = (int32_t)pair_cap; da.bulk = 0;
   cusim::launch(dim3(grid), dim3(32 * warps), (size_t)da.wstride * warps, [&] { k_decode<false>(da); });
   if (zstd_ok) {
     da.base = base.data() + (n + 1);
