@@ -118,11 +118,14 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
     bool live[4], nlive[4];
     auto fetch = [&](int gb, uint32_t* fs, uint32_t* fh, unsigned* fp, bool* fl) {
       const int bbase = tbase + gb * 32;
+      // the 4 bytes at bbase + 32 j + lane: `in` is word aligned and bbase a multiple of 32, so every lane's two words and
+      // its shift are known without address arithmetic (positions beyond plimit read the window's slack, masked by fl)
+      const uint32_t* wb = (const uint32_t*)(in + bbase) + (lane >> 2);
+      const unsigned sh = (unsigned)(lane & 3) * 8u;
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        const int p = bbase + 32 * j + lane;
-        fl[j] = p <= plimit;
-        fs[j] = ld32_any(in + (fl[j] ? p : 0));
+        fl[j] = bbase + 32 * j + lane <= plimit;
+        fs[j] = __funnelshift_r(wb[8 * j], wb[8 * j + 1], sh);
         fh[j] = (fs[j] * 2654435761u) >> (32 - w.hlog);
       }
 #pragma unroll

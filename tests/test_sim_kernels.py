@@ -377,6 +377,25 @@ def test_compress_batch_lookback_many_ctas():
     assert res[3][1].size == srcs[3].size + 32 and (res[3][1][2] & 2)  # noise -> memcpyed chunk
 
 
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+@pytest.mark.parametrize("clevel", [1, 3, 5, 6, 8, 9])
+def test_compress_levels_decodable_by_checker(codec, clevel):
+    """The encoder's effort follows the level (b2g_plan.h: table size, shortest match worth a sequence, the margin under
+    which a stream is stored): whatever the level, the reference / the oracle decode the chunk and so does the kernel."""
+    sizes = []
+    for ts, kinds in ((2, ("half", "sensor", "text")), (1, ("ramp", "longrun")), (4, ("f32",))):
+        srcs = [_data.make_data(k, 150000 + 4 * i, ts, seed=7 + i) for i, k in enumerate(kinds)]
+        res = _sim.compress_batch(srcs, codec, clevel, ts, _data.SHUFFLE, 32768)
+        for s, (st, chunk) in zip(srcs, res):
+            assert st == 0
+            rc, back = _checker_decompress(chunk)
+            assert rc == s.size and np.array_equal(back, s), (clevel, ts)
+            sizes.append(chunk.size)
+        for s, (st, out) in zip(srcs, _sim.decompress_batch([c for _, c in res])):
+            assert st == 0 and np.array_equal(out, s)
+    assert sum(sizes) < 6 * 150100 * 0.9          # every level still compresses this data
+
+
 def test_compress_capacity_rules():
     src = _data.make_data("random", 50000, 1)
     (st, chunk), = _sim.compress_batch([src], _data.LZ4, 5, 1, _data.SHUFFLE, 32768, caps=[50000 + 31])
