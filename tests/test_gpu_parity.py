@@ -339,3 +339,36 @@ def test_every_compression_level_is_reference_decodable(codec, ts):
         sizes[clevel] = total
     assert sizes[9] <= min(sizes.values()) * 1.002
     assert sizes[1] <= sizes[9] * 1.12          # the fast levels give up a few per cent, not the compression
+
+
+def test_staged_host_path_reports_per_chunk_errors_like_the_direct_path():
+    """A batch in pageable memory large enough for the staging threads (several sub-batches) with damaged chunks in it: every
+    chunk gets the status and the bytes it gets when it is decoded alone (one sub-batch: the direct path), good chunks are
+    untouched by their neighbours' failures, and a compress batch through the same path round-trips."""
+    from compressed_image_b200 import _b2g
+    n, nb = 10, 4 << 20
+    srcs = [_data.make_data(k, nb, 2, seed=i) for i, k in enumerate(("half", "sensor", "text", "ramp", "half") * 2)]
+    with _b2g.Context(_b2g.LZ4, 9, 2, _b2g.SHUFFLE, 32768, 0) as cx:
+        chunks = cx.compress(srcs)                       # 40 MiB of pageable input: staged
+        for c, s in zip(chunks, srcs):
+            rc, back = _checker_decompress(c)
+            assert rc == nb and np.array_equal(back, s)
+        bad = [c.copy() for c in chunks]
+        bad[2][4:8] = np.frombuffer(np.int32(-4).tobytes(), np.uint8)        # negative nbytes
+        bad[5] = bad[5][:bad[5].size // 2].copy()                            # truncated
+        bad[7][40:44] = 0xFF                                                 # a bstarts entry out of range
+        outs = [np.full(nb, 0xAB, np.uint8) for _ in range(n)]
+        b = cx.make_batch([c.ctypes.data for c in bad], [o.ctypes.data for o in outs], [int(c.size) for c in bad], [nb] * n)
+        cx.decompress_batch(b)
+        alone = []
+        for c in bad:
+            o = np.full(nb, 0xAB, np.uint8)
+            b1 = cx.make_batch([c.ctypes.data], [o.ctypes.data], [int(c.size)], [nb])
+            cx.decompress_batch(b1)
+            alone.append((b1[0].status, b1[0].out_bytes))
+        for i in range(n):
+            assert (b[i].status, b[i].out_bytes) == alone[i], i
+            if i in (2, 5, 7):
+                assert b[i].status < 0 and b[i].out_bytes == 0
+            else:
+                assert b[i].status == 0 and np.array_equal(outs[i], srcs[i]), i
