@@ -157,7 +157,7 @@ struct b2g_ctx {
 namespace {
 
 std::mutex g_attr_mutex;
-size_t g_smem_limit[64][12];  // [device][kernel]
+size_t g_smem_limit[64][16];  // [device][kernel]
 
 int raise_smem_limit(int dev, int which, const void* fn, size_t bytes) {
   std::lock_guard<std::mutex> lock(g_attr_mutex);
@@ -175,11 +175,39 @@ size_t slab_stride(const b2g_ctx* c);
 constexpr int kMaxEncoderStream = 192 * 1024;  // window + 8 KiB table + work area must fit 227 KiB
 struct CompGeom {
   int win, htab, warps, grid, tile, which;
+  int team, prime;        // team > 1: k_compress_team, one stream per CTA of `team` warps
+  size_t scratch_stride;  // per stream item
   const void* fn;
   size_t smem;
 };
+// Experiment switches for the encoder teams: B2G_TEAM = 0 / 1 one warp per stream for every batch, N > 1 teams of N;
+// B2G_TEAM_PRIME = positions primed in front of a segment; B2G_TEAM_HLOG = log2 of the per-warp table entries.
+static const int g_team_env = [] { const char* e = getenv("B2G_TEAM"); return e ? atoi(e) : -1; }();
+static const int g_team_prime_env = [] { const char* e = getenv("B2G_TEAM_PRIME"); return e ? atoi(e) : -1; }();
+static const int g_team_hlog_env = [] { const char* e = getenv("B2G_TEAM_HLOG"); return e ? atoi(e) : 0; }();
+
 int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   g.win = std::max((int)align_up((size_t)std::max(max_stream, 1), 16), 1024);
+  g.team = g_team_env < 0 ? plan_team_warps(max_stream) : std::min(std::max(g_team_env, 1), (int)kTeamMaxWarps);
+  g.prime = 0;
+  g.scratch_stride = (size_t)g.win;  // an encoded stream is kept only when it is smaller than the stream
+  const bool lz4codec = c->p.codec == B2G_LZ4 || c->p.codec == B2G_LZ4HC;
+  if (g.team > 1) {
+    g.prime = g_team_prime_env < 0 ? kTeamPrime : (g_team_prime_env + 127) / 128 * 128;
+    g.tile = kTeamTile;
+    g.htab = g_team_hlog_env > 0 ? (2 << std::min(std::max(g_team_hlog_env, 6), 12)) : plan_htab_bytes(max_stream, c->p.clevel);
+    g.warps = g.team;
+    g.smem = (size_t)g.win + (size_t)g.team * ((size_t)g.htab + (size_t)enc_work_bytes(g.tile)) + sizeof(TeamCtl);
+    if (g.smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
+    g.scratch_stride = (size_t)plan_team_scratch_stride(g.win);
+    g.which = lz4codec ? 4 : 5;
+    g.fn = lz4codec ? (const void*)k_compress_team<kCodecLz4, kTeamTile> : (const void*)k_compress_team<kCodecBlosclz, kTeamTile>;
+    if (int rc = raise_smem_limit(c->dev, 8 + g.which, g.fn, g.smem)) return rc;   // slots 12, 13
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, g.fn, 32 * g.warps, g.smem));
+    g.grid = c->sms * std::max(occ, 1);
+    return 0;
+  }
   g.htab = plan_htab_bytes(max_stream, c->p.clevel);
   g.tile = enc_tile_for(max_stream);
   const size_t per = (size_t)g.win + (size_t)g.htab + (size_t)enc_work_bytes(g.tile);
@@ -394,7 +422,7 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   base[n] = (int32_t)items;
   CompGeom g;
   if (int rc = compress_geometry(c, max_stream, g)) return rc;
-  const size_t scratch_stride = (size_t)g.win;  // an encoded stream is kept only when it is smaller than the stream
+  const size_t scratch_stride = g.scratch_stride;
   if (int rc = L.d_items.ensure(sizeof(CItem) * (size_t)items)) return rc;
   if (int rc = L.d_scratch.ensure(scratch_stride * (size_t)items + 256)) return rc;
   if (int rc = L.d_chunks.ensure(sizeof(DChunk) * (size_t)n)) return rc;
@@ -427,8 +455,9 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.win_bytes = g.win;
   ca.htab_bytes = g.htab;
   ca.tile = g.tile;
+  ca.team_prime = g.prime;
   ca.p = cp;
-  const int cgrid = (int)std::min<int64_t>(g.grid, (items + g.warps - 1) / g.warps);
+  const int cgrid = (int)std::min<int64_t>(g.grid, g.team > 1 ? items : (items + g.warps - 1) / g.warps);
   {
     void* kargs[] = {(void*)&ca};
     CU(cudaLaunchKernel(g.fn, dim3((unsigned)cgrid), dim3((unsigned)(32 * g.warps)), kargs, g.smem, s));

@@ -20,6 +20,15 @@ constexpr int kMinBuffer = 32;         // b2h:193 BLOSC_MIN_BUFFERSIZE
 constexpr int kMaxBlocksize = 536866816;
 constexpr int kCtaThreads = 128;       // every block-level kernel runs 4 warps per CTA
 constexpr int kCtaWarps = kCtaThreads / 32;
+// encoder teams (k_compress_team, b2g_plan.h): bytes of a stream per warp, warps per team, encoder tile, and how
+// many positions in front of its segment a warp's hash table is primed with.  Measured on 32 KiB streams (cfg 1: LZ4
+// on unsplit uint8 blocks; cfg 3: blosclz on bit-shuffled blocks): four warps x 8 KiB primed with the 8 KiB in front
+// compress 2.07x / 1.47x faster than one warp per stream at -0.3 % / +0.3 % ratio; 4 KiB segments or less priming
+// are faster still but cost 2-4 % ratio.  On 16 KiB streams two warps gain nothing and four cost 0.55 % ratio for 8 %.
+constexpr int kTeamSegment = 8192;
+constexpr int kTeamMaxWarps = 8;
+constexpr int kTeamTile = 512;
+constexpr int kTeamPrime = 8192;
 constexpr unsigned kFull = 0xffffffffu;
 
 enum : uint8_t { kFlagShuffle = 1, kFlagMemcpyed = 2, kFlagBitshuffle = 4, kFlagDelta = 8, kFlagDontSplit = 0x10 };

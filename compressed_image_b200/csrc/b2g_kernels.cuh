@@ -653,6 +653,7 @@ struct CompressArgs {
   int32_t htab_bytes;            // per-warp hash table bytes (a power of two); each warp's work area is
                                  // htab_bytes + enc_work_bytes(tile), see enc_work()
   int32_t tile;                  // encoder tile (positions), enc_tile_for(largest stream of the batch)
+  int32_t team_prime;            // k_compress_team: positions in front of a segment that prime its hash table
   CParams p;
 };
 
@@ -778,6 +779,91 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
     }
     if (lane == 0) a.items[item] = r;
     __syncwarp();  // the window is free for the next item
+  }
+}
+
+// The same work item encoded by a TEAM: the CTA's warps share one window and encode consecutive segments of the stream
+// side by side (lz_encode_warp<SEG>), then join their bodies into the item's scratch slot (lz_join_team).  A 16 KiB
+// plane keeps four warps busy for one window instead of one, so the SM holds as many warps as its registers allow
+// instead of as many as 227 KiB / (window + table) -- the encoder is a latency-bound dependent chain, more resident
+// warps are what it lacks.  Costs: a match may not cross a segment boundary, and a segment's table only knows the
+// team_prime positions in front of it (ratio: see DESIGN.md); every item costs five CTA barriers.
+// Scratch slot of an item: [win_bytes joined stream][S bodies of team_body_stride(segment) bytes].
+struct TeamCtl {
+  EncSeg seg[kTeamMaxWarps];
+  int32_t item;
+  int32_t notrun;
+};
+
+template <int CODEC, int TILE>
+__global__ void __launch_bounds__(256, 2) k_compress_team(CompressArgs a) {
+  const int warp = warp_id(), lane = lane_id(), tid = (int)threadIdx.x, nthr = (int)blockDim.x, S = nthr >> 5;
+  const int wbytes = a.htab_bytes + enc_work_bytes(TILE);
+  uint8_t* win = dyn_smem();                                      // [win_bytes] the filtered stream, the whole team's
+  uint8_t* work = win + a.win_bytes + (size_t)warp * (size_t)wbytes;
+  TeamCtl* tc = (TeamCtl*)(win + a.win_bytes + (size_t)S * (size_t)wbytes);
+  const int ts = a.p.typesize;
+  int hint = 0;
+  for (;;) {
+    __syncthreads();  // the team is done with the previous item: window, segment records, flags
+    if (tid == 0) { tc->item = atomicAdd(&a.ctl->ticket, 1); tc->notrun = 0; }
+    __syncthreads();
+    const int item = tc->item;
+    if (item >= a.ctl->total_items) break;
+    const int c = find_chunk(a.base, a.n, item, hint);
+    hint = c;
+    const CInfo d = a.info[c];
+    const int it = item - d.item_base;
+    if (d.status < 0 || d.memcpyed || it >= d.nitems) continue;  // k_finalize stores these chunks
+    const StreamGeom g = stream_geometry(d, ts, it);
+    const uint8_t* raw = a.chunks[c].src + (size_t)g.j * d.blocksize;
+    if (g.ns > 1) gather_plane(ts, g.s, g.neblock, raw, win, tid, nthr);
+    else filter_forward(a.p.filter, ts, g.bsize, raw, win, tid, nthr);
+    __syncthreads();
+    const int n = g.neblock;
+    const int seglen = team_segment_len(n, S, TILE);
+    const int sb = warp * seglen, se = min(n, sb + seglen);
+    const bool same = sb >= n || (win[sb] == win[0] && warp_is_run(win + sb, se - sb, lane));
+    if (!same && lane == 0) tc->notrun = 1;
+    __syncthreads();
+    CItem r;
+    r.offset = 0;
+    r.stored = 0;
+    if (!tc->notrun) {
+      const uint8_t v = win[0];
+      r.csize = -(int32_t)v;
+      r.psize = v ? 1 : 0;
+    } else {
+      const int cap = n - 1;  // only a strictly smaller result is worth keeping (blosc2.c:1204-1211)
+      int total = 0;
+      if (CODEC != kCodecBlosclz || (n >= 16 && cap >= 66)) {  // blosclz.c:480-482
+        int hlog = 28 - __clz(n);   // as k_compress: floor(log2(n)) - 3, at most what the host's table size allows
+        const int hmax = 30 - __clz(a.htab_bytes);
+        hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
+        const EncWork ew = enc_work(work, a.htab_bytes, hlog, TILE, CODEC == kCodecBlosclz || a.p.clevel > 5 ? 4 : (a.p.clevel > 2 ? 5 : 6));
+        uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
+        uint8_t* bodies = out + a.win_bytes;
+        const int bstride = team_body_stride(seglen);
+        if (sb < n) {
+          lz_encode_warp<CODEC, TILE, true>(win, n, bodies + (size_t)warp * (size_t)bstride, bstride, ew, sb, se, a.team_prime,
+                                            &tc->seg[warp]);
+        } else if (lane == 0) {
+          tc->seg[warp].p0 = -1;
+          tc->seg[warp].bytes = 0;
+          tc->seg[warp].end = 0;
+        }
+        __syncthreads();
+        total = lz_join_team<CODEC>(win, n, tc->seg, S, bodies, bstride, out, cap, warp, lane);
+        if (CODEC == kCodecBlosclz && total > 0) {
+          __syncthreads();
+          if (tid == 0) out[0] |= 32;  // codec marker (blosclz.c:613)
+        }
+      }
+      const int margin = a.p.clevel >= 9 ? 0 : (a.p.clevel >= 6 ? n >> 7 : (a.p.clevel >= 3 ? n >> 6 : n >> 5));
+      if (total <= 0 || total >= n - margin) { r.stored = 1; r.psize = r.csize = n; }
+      else r.psize = r.csize = total;
+    }
+    if (tid == 0) a.items[item] = r;
   }
 }
 

@@ -71,30 +71,113 @@ __device__ __forceinline__ int lz4_put_ext_lane(uint8_t* out, int op, int v) {  
   return op;
 }
 
+// The encoder reads its input through a shared-space view (MemShared: ld.shared with 32-bit addresses; through a plain
+// generic pointer every access is a 64-bit generic load -- LD, not LDS -- with the address arithmetic to match).
+using EncIn = MemSel<true>::type;
+// 4 bytes at any position (the view's byte 0 is word aligned; reads up to 4 bytes beyond: the window's slack)
+__device__ __forceinline__ uint32_t enc_ld32(const EncIn& I, int i) {
+  const unsigned sh = (unsigned)(i & 3) * 8u;
+  const int a = i & ~3;
+  return __funnelshift_r(I.ld32(a), I.ld32(a + 4), sh);
+}
+// Number of equal bytes of I[a..a+maxlen) and I[b..b+maxlen), compared warp-wide 32 x 4 bytes per round.
+__device__ __forceinline__ int enc_match_len(const EncIn& I, int a, int b, int maxlen, int lane) {
+  int done = 0;
+  while (done < maxlen) {
+    const int i = done + lane * 4;
+    const int rem = maxlen - i;
+    unsigned neq = enc_ld32(I, a + i) ^ enc_ld32(I, b + i);
+    if (rem < 4) neq = rem <= 0 ? 0xffffffffu : (neq | (0xffffffffu << (8 * rem)));
+    const unsigned m = __ballot_sync(kFull, neq != 0);
+    if (m) {
+      const int l = __ffs((int)m) - 1;
+      const unsigned x = __shfl_sync(kFull, neq, l);
+      const int n = done + l * 4 + ((__ffs((int)x) - 1) >> 3);
+      return n < maxlen ? n : maxlen;
+    }
+    done += 128;
+  }
+  return maxlen;
+}
+// blosclz literal runs (blosclz_put_literals) with the input behind a view
+__device__ __forceinline__ int enc_blz_literals(const EncIn& I, int anchor, int lit, uint8_t* out, int op, int lane) {
+  const int groups = (lit + 31) >> 5;
+  const int total = lit + groups;
+  for (int k = lane; k < total; k += 32) {
+    const int g = k / 33, w = k - g * 33;
+    uint32_t v;
+    if (w == 0) {
+      const int left = lit - (g << 5);
+      v = (uint32_t)((left > 32 ? 32 : left) - 1);
+    } else {
+      v = I.ld8(anchor + (g << 5) + w - 1);
+    }
+    out[op + k] = (uint8_t)v;
+  }
+  return op + total;
+}
+
 constexpr int kEncSelfLit = 16;  // literal runs up to this length are copied by the sequence's own lane
+
+// What one warp of a TEAM reports about its segment of a stream (k_compress_team: several warps encode consecutive
+// segments of one stream side by side).  A segment's output is a BODY: its sequences without the literal run in front
+// of the first match (LZ4: without that sequence's token either, the body starts with its offset field), because where
+// that run starts is the end of the previous segment's last match.  lz_join_team() writes those pieces.
+struct EncSeg {
+  int32_t p0;     // start of the segment's first match, -1 = the segment has no sequence
+  int32_t ml0;    // length of that match (LZ4: goes into the token the join writes)
+  int32_t end;    // end of the segment's last match
+  int32_t bytes;  // body bytes, -1 = the body did not fit its slot
+};
 
 // Compresses in[0..n) (shared memory) into out[0..cap) (global or shared).  Returns the compressed size, or 0 when
 // the result does not fit in cap / the stream is too small for the codec (the caller then stores the stream raw, as
 // blosc_c does: blosc2.c:1288-1324).  All 32 lanes call with identical arguments.
-template <int CODEC, int TILE>
-__device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t* out, int cap, const EncWork& w) {
+//
+// SEG = the warp encodes the SEGMENT [seg_begin, seg_end) of the stream (seg_begin a multiple of the tile; matches start
+// and end inside the segment, their sources lie anywhere before them) and writes a body (EncSeg) instead of a stream:
+// the hash table is primed with the `prime` positions in front of the segment (a multiple of 128), the first sequence
+// loses its literal run, there is no closing run.  Returns the body bytes, -1 when they do not fit in cap.
+template <int CODEC, int TILE, bool SEG = false>
+__device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t* out, int cap, const EncWork& w,
+                                              int seg_begin = 0, int seg_end = 0, int prime = 0, EncSeg* seg = nullptr) {
   constexpr bool LZ4 = CODEC == kCodecLz4;
   const int lane = lane_id();
+  const EncIn I(in);
+  const MemGeneric O(out);
   int plimit, mlimit;  // last position a match may start at; matches end at or before mlimit
   if (LZ4) {
     plimit = n - 12;   // lz4.c:245-249 (MFLIMIT 12, LASTLITERALS 5)
     mlimit = n - 5;
   } else {
-    if (n < 16 || cap < 66) return 0;  // blosclz.c:480-482
+    if (!SEG && (n < 16 || cap < 66)) return 0;  // blosclz.c:480-482 (a team checks the whole stream)
     plimit = n - 13;
     mlimit = n - 4;
   }
+  if (SEG) {
+    plimit = min(plimit, seg_end - 4);
+    mlimit = min(mlimit, seg_end);
+    if (lane == 0) seg->p0 = -1;
+  }
   for (int i = lane; i < (1 << w.hlog); i += 32) w.htab[i] = 0;
   __syncwarp();
-  int anchor = 0, ip = 0, op = 0, step = 1;
+  if (SEG) {  // positions in front of the segment: inserted, never probed (whichever lane wins a slot is a valid candidate)
+    for (int pb = max(0, seg_begin - prime); pb < seg_begin; pb += 128) {
+      const int wb = pb + 4 * (lane >> 2);
+      const unsigned sh = (unsigned)(lane & 3) * 8u;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const uint32_t s4 = __funnelshift_r(I.ld32(wb + 32 * j), I.ld32(wb + 32 * j + 4), sh);
+        w.htab[(s4 * 2654435761u) >> (32 - w.hlog)] = (uint16_t)(pb + 32 * j + lane);
+        __syncwarp();  // later groups overwrite earlier ones
+      }
+    }
+  }
+  int anchor = SEG ? seg_begin : 0, ip = anchor, op = 0, step = 1;
+  bool head_pending = SEG;  // the segment's first sequence is still to come
   const unsigned lt_mask = (1u << lane) - 1u;
   constexpr int kEncTile = TILE, kEncGroups = TILE / 32;   // == w.tile (the work area is laid out for it)
-  for (int tbase = 0; tbase <= plimit; tbase += kEncTile) {
+  for (int tbase = SEG ? seg_begin : 0; tbase <= plimit; tbase += kEncTile) {
     if (ip >= tbase + kEncTile) continue;  // the tile lies inside an earlier match
     // ---- phase 1: candidates ----------------------------------------------------------------------------------
     // Four groups of 32 positions per step, as four independent dependency chains (the step is latency-bound, not
@@ -120,12 +203,12 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       const int bbase = tbase + gb * 32;
       // the 4 bytes at bbase + 32 j + lane: `in` is word aligned and bbase a multiple of 32, so every lane's two words and
       // its shift are known without address arithmetic (positions beyond plimit read the window's slack, masked by fl)
-      const uint32_t* wb = (const uint32_t*)(in + bbase) + (lane >> 2);
+      const int wb = bbase + 4 * (lane >> 2);
       const unsigned sh = (unsigned)(lane & 3) * 8u;
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         fl[j] = bbase + 32 * j + lane <= plimit;
-        fs[j] = __funnelshift_r(wb[8 * j], wb[8 * j + 1], sh);
+        fs[j] = __funnelshift_r(I.ld32(wb + 32 * j), I.ld32(wb + 32 * j + 4), sh);
         fh[j] = (fs[j] * 2654435761u) >> (32 - w.hlog);
       }
 #pragma unroll
@@ -150,7 +233,7 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         const uint32_t pseq = __shfl_sync(kFull, seq[j], src);
         int c = p - (int)((uint32_t)(p - (int)tab[j]) & 0xffffu);   // table candidate, within 65535 of p
         const bool tab_ok = c >= 0 && c < p;
-        const uint32_t cseq = ld32_any(in + (tab_ok ? c : 0));
+        const uint32_t cseq = enc_ld32(I, tab_ok ? c : 0);
         bool ok;
         if (prev) {  // the most recent earlier position with this hash is in this very group
           c = bbase + 32 * j + src;
@@ -194,18 +277,18 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       // the bytes in front of the match and of its source, for the backward extension below: fetched here so that their
       // latency overlaps the forward compare
       const bool can_back = p > lastend && c > 0;
-      const uint32_t pb = in[can_back ? p - 1 : 0], cb = in[can_back ? c - 1 : 0];
+      const uint32_t pb = I.ld8(can_back ? p - 1 : 0), cb = I.ld8(can_back ? c - 1 : 0);
       // Match length beyond the verified 4 bytes.  Most matches of a noisy plane end within the next 4 bytes: one
       // warp-uniform word compare settles those, the warp-wide compare only runs for the longer ones (same result).
       int ml;
       {
         const int room = mlimit - (p + 4);
-        const uint32_t x = ld32_any(in + p + 4) ^ ld32_any(in + c + 4);  // p + 7 <= n - 5: inside the stream
+        const uint32_t x = enc_ld32(I, p + 4) ^ enc_ld32(I, c + 4);  // p + 7 <= n - 5: inside the stream
         if (x != 0u || room <= 4) {
           const int e = x ? ((__ffs((int)x) - 1) >> 3) : 4;
           ml = 4 + max(0, min(e, room));
         } else {
-          ml = 8 + warp_match_len(in + p + 8, in + c + 8, room - 4, lane);
+          ml = 8 + enc_match_len(I, p + 8, c + 8, room - 4, lane);
         }
       }
       if (!LZ4 && dist - 1 >= kBlzMaxDistance && ml < 8) {  // a 4-byte far token does not pay for a short match
@@ -220,7 +303,7 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       }
       if (can_back && pb == cb) {  // extend over pending literals
         p--; c--; ml++;
-        while (p > lastend && c > 0 && in[p - 1] == in[c - 1]) { p--; c--; ml++; }
+        while (p > lastend && c > 0 && I.ld8(p - 1) == I.ld8(c - 1)) { p--; c--; ml++; }
       }
       if (lane == 0) { w.sp[nseq] = (uint32_t)p; w.sml[nseq] = (uint32_t)ml; w.so[nseq] = (uint16_t)dist; }
       nseq++;
@@ -239,12 +322,13 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         dist = (int)w.so[i];
         start = i == 0 ? anchor : (int)(w.sp[i - 1] + w.sml[i - 1]);
       }
-      const int lit = p - start;
+      const bool head = SEG && head_pending && i == 0;       // its literal run (LZ4: and token) belong to the join
+      const int lit = head ? 0 : p - start;
       const int L = ml - 2;                                  // blosclz length code
       const bool far = dist - 1 >= kBlzMaxDistance;          // blosclz far match
       int size = 0;
       if (have) {
-        if (LZ4) size = 1 + lz4_ext_bytes(lit) + lit + 2 + lz4_ext_bytes(ml - 4);
+        if (LZ4) size = (head ? 0 : 1 + lz4_ext_bytes(lit) + lit) + 2 + lz4_ext_bytes(ml - 4);
         else size = lit + ((lit + 31) >> 5) + 1 + (L >= 7 ? (L - 7) / 255 + 1 : 0) + (far ? 3 : 1);
       }
       int incl = size;
@@ -254,17 +338,23 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         if (lane >= o) incl += t;
       }
       const int total = __shfl_sync(kFull, incl, 31);
-      if (op + total > cap) return 0;  // limited output, like LZ4_compress_fast with maxOutputSize (lz4.c:1453)
+      if (op + total > cap) {          // limited output, like LZ4_compress_fast with maxOutputSize (lz4.c:1453)
+        if (SEG && lane == 0) seg->bytes = -1;
+        return SEG ? -1 : 0;
+      }
       int q = op + incl - size;        // where this lane's sequence starts
       int litpos = 0;
       if (have) {
+        if (head) { seg->p0 = p; seg->ml0 = ml; }
         if (LZ4) {
-          out[q++] = (uint8_t)(((lit >= 15 ? 15 : lit) << 4) | (ml - 4 >= 15 ? 15 : ml - 4));
-          if (lit >= 15) q = lz4_put_ext_lane(out, q, lit);
-          litpos = q;
-          if (lit <= kEncSelfLit)
-            for (int k = 0; k < lit; k++) out[q + k] = in[start + k];
-          q += lit;
+          if (!head) {
+            out[q++] = (uint8_t)(((lit >= 15 ? 15 : lit) << 4) | (ml - 4 >= 15 ? 15 : ml - 4));
+            if (lit >= 15) q = lz4_put_ext_lane(out, q, lit);
+            litpos = q;
+            if (lit <= kEncSelfLit)
+              for (int k = 0; k < lit; k++) out[q + k] = (uint8_t)I.ld8(start + k);
+            q += lit;
+          }
           out[q] = (uint8_t)dist;
           out[q + 1] = (uint8_t)(dist >> 8);
           q += 2;
@@ -273,7 +363,7 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
           litpos = q;
           if (lit > 0 && lit <= kEncSelfLit) {
             out[q] = (uint8_t)(lit - 1);
-            for (int k = 0; k < lit; k++) out[q + 1 + k] = in[start + k];
+            for (int k = 0; k < lit; k++) out[q + 1 + k] = (uint8_t)I.ld8(start + k);
           }
           q += lit + ((lit + 31) >> 5);
           const int db = dist - 1;
@@ -300,19 +390,24 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
         const int s = __shfl_sync(kFull, start, j), d = __shfl_sync(kFull, litpos, j), l = __shfl_sync(kFull, lit, j);
         if (LZ4) {
           if (l <= 64) {  // the usual case: one or two bytes per lane, no alignment bookkeeping
-            if (lane < l) out[d + lane] = in[s + lane];
-            if (lane + 32 < l) out[d + 32 + lane] = in[s + 32 + lane];
+            if (lane < l) out[d + lane] = (uint8_t)I.ld8(s + lane);
+            if (lane + 32 < l) out[d + 32 + lane] = (uint8_t)I.ld8(s + 32 + lane);
           } else {
-            copy_bytes(out + d, in + s, l, lane, 32);
+            warp_copy(I, s, O, d, l, lane);
           }
         } else {
-          blosclz_put_literals(in, s, l, out, d, lane);
+          enc_blz_literals(I, s, l, out, d, lane);
         }
       }
       op += total;
     }
-    if (nseq) anchor = lastend;
+    if (nseq) { anchor = lastend; head_pending = false; }
     __syncwarp();
+  }
+  if (SEG) {
+    if (lane == 0) { seg->end = anchor; seg->bytes = op; }
+    __syncwarp();
+    return op;
   }
   // ---- closing literal run --------------------------------------------------------------------------------------------
   const int lit = n - anchor;
@@ -323,16 +418,76 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
       if (lit >= 15) lz4_put_ext_lane(out, op + 1, lit);
     }
     op += 1 + lz4_ext_bytes(lit);
-    copy_bytes(out + op, in + anchor, lit, lane, 32);
+    warp_copy(I, anchor, O, op, lit, lane);
     op += lit;
   } else {
     if (op + lit + ((lit + 31) >> 5) > cap) return 0;
-    op = blosclz_put_literals(in, anchor, lit, out, op, lane);
+    op = enc_blz_literals(I, anchor, lit, out, op, lane);
     __syncwarp();
     if (lane == 0) out[0] |= 32;  // codec marker (blosclz.c:613)
   }
   __syncwarp();
   return op;
+}
+
+// Segment of warp `warp` of a team of S for a stream of n bytes: [begin, begin + len) with len a multiple of the tile.
+__device__ __forceinline__ int team_segment_len(int n, int S, int tile) { return ((n + S - 1) / S + tile - 1) / tile * tile; }
+__device__ __forceinline__ int team_body_stride(int seglen) { return seglen + 64; }
+
+// The team's join: every thread of the S warps calls it with the same arguments (but its own warp / lane) after the team
+// has synchronised on the segment records.  Lays the stream out -- for every segment with a sequence: the literal run
+// from the end of the previous segment's last match to its first match (LZ4: under the token that also carries that
+// match's length), then its body; the closing literal run -- and, when it fits in cap, writes it: each warp its own
+// segment's run and body (body k lies at bodies + k * body_stride, written by this very warp), the last warp the
+// closing run.  Returns the stream's size, 0 when it does not fit or a body overflowed.  (blosclz: the caller sets the
+// marker bit of out[0] once the team has synchronised again.)
+template <int CODEC>
+__device__ __forceinline__ int lz_join_team(const uint8_t* in, int n, const EncSeg* segs, int S, const uint8_t* bodies,
+                                            int body_stride, uint8_t* out, int cap, int warp, int lane) {
+  constexpr bool LZ4 = CODEC == kCodecLz4;
+  const EncIn I(in);
+  const MemGeneric O(out);
+  int prev = 0, pos = 0, my_start = 0, my_lit = -1, my_pos = 0;
+  for (int k = 0; k < S; k++) {
+    const int p0 = segs[k].p0, bytes = segs[k].bytes;
+    if (bytes < 0) return 0;
+    if (p0 < 0) continue;
+    const int lit = p0 - prev;
+    if (k == warp) { my_start = prev; my_lit = lit; my_pos = pos; }
+    pos += (LZ4 ? 1 + lz4_ext_bytes(lit) + lit : lit + ((lit + 31) >> 5)) + bytes;
+    prev = segs[k].end;
+  }
+  const int clit = n - prev;
+  const int total = pos + (LZ4 ? 1 + lz4_ext_bytes(clit) + clit : clit + ((clit + 31) >> 5));
+  if (total > cap) return 0;
+  if (my_lit >= 0) {
+    int q = my_pos;
+    if (LZ4) {
+      const int m = segs[warp].ml0 - 4;
+      if (lane == 0) {
+        out[q] = (uint8_t)(((my_lit >= 15 ? 15 : my_lit) << 4) | (m >= 15 ? 15 : m));
+        if (my_lit >= 15) lz4_put_ext_lane(out, q + 1, my_lit);
+      }
+      q += 1 + lz4_ext_bytes(my_lit);
+      warp_copy(I, my_start, O, q, my_lit, lane);
+      q += my_lit;
+    } else {
+      q = enc_blz_literals(I, my_start, my_lit, out, q, lane);
+    }
+    copy_bytes(out + q, bodies + (size_t)warp * (size_t)body_stride, segs[warp].bytes, lane, 32);
+  }
+  if (warp == S - 1) {
+    if (LZ4) {
+      if (lane == 0) {
+        out[pos] = (uint8_t)((clit >= 15 ? 15 : clit) << 4);
+        if (clit >= 15) lz4_put_ext_lane(out, pos + 1, clit);
+      }
+      warp_copy(I, prev, O, pos + 1 + lz4_ext_bytes(clit), clit, lane);
+    } else {
+      enc_blz_literals(I, prev, clit, out, pos, lane);
+    }
+  }
+  return total;
 }
 
 }  // namespace b2g

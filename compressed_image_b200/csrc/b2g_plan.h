@@ -78,4 +78,15 @@ inline int plan_htab_bytes(int neblock, int clevel = 9) {
   return 2 << hlog;
 }
 
+// Encoder teams (k_compress_team): streams above two segments are encoded by several warps of one CTA side by side, each
+// warp a segment of the stream in the CTA's one shared-memory window.  Warps per team for a batch whose largest stream
+// is `max_stream` bytes (1 = every warp its own stream, k_compress), the segment of a `neblock`-byte stream (a multiple
+// of the encoder tile), the positions in front of a segment its hash table is primed with, and the scratch slot of one
+// stream item: the joined stream (< win bytes) followed by the segments' bodies (segment + 64 bytes each).
+inline int plan_team_warps(int max_stream) {
+  if (max_stream <= 2 * kTeamSegment) return 1;
+  return std::min(kTeamMaxWarps, (max_stream + kTeamSegment - 1) / kTeamSegment);
+}
+inline int plan_team_scratch_stride(int win) { return 2 * win + kTeamMaxWarps * (kTeamTile + 64); }
+
 }  // namespace b2g

@@ -89,6 +89,15 @@ def compress_batch(srcs, codec, clevel, typesize, filt, blocksize, caps=None, wi
     return res
 
 
+def set_team(warps=-1, prime=-1, hlog=0):
+    """Encoder teams in sim_compress_batch: warps -1 = as the library decides (plan_team_warps), 0 / 1 = one warp per
+    stream (k_compress), N > 1 = k_compress_team with N warps; prime -1 = the library's default."""
+    L = lib()
+    L.sim_set_team.argtypes = [C.c_int] * 3
+    L.sim_set_team.restype = None
+    L.sim_set_team(warps, prime, hlog)
+
+
 def run_filter(filt, forward, typesize, src, blocksize, version=5, grid=2):
     src = np.ascontiguousarray(src)
     dst = np.zeros(src.size + 16, dtype=np.uint8)

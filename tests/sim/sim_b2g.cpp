@@ -11,6 +11,9 @@ using namespace b2g;
 static size_t au(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static int g_last_paired = 0;
+// encoder teams: -1 = as the host library decides (plan_team_warps), 0 / 1 = k_compress (one warp per stream), S > 1 =
+// k_compress_team with S warps; prime < 0 = kTeamPrime
+static int g_team = -1, g_team_prime = -1, g_team_hlog = 0;
 
 extern "C" {
 
@@ -98,26 +101,40 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   ctl[0].total_items = (int32_t)items;
   const int warps = 2;  // independent workers per simulated CTA
   const int wwin = std::max((int)au(max_stream, 16), 1024);
+  const int team = g_team < 0 ? plan_team_warps(max_stream) : std::min(g_team, (int)kTeamMaxWarps);
+  const size_t sstride = team > 1 ? (size_t)plan_team_scratch_stride(wwin) : (size_t)wwin;
   std::vector<CItem> citems(items + 1);
-  std::vector<uint8_t> scratch((size_t)wwin * items + 256);
+  std::vector<uint8_t> scratch(sstride * items + 256);
   CompressArgs ca;
   ca.chunks = ch.data(); ca.info = info.data(); ca.state = state.data(); ca.base = base.data(); ca.ctl = ctl;
-  ca.items = citems.data(); ca.scratch = scratch.data(); ca.scratch_stride = wwin; ca.n = n;
-  const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);
-  ca.win_bytes = wwin; ca.htab_bytes = htab_bytes; ca.p = p;
-  ca.tile = enc_tile_for(max_stream);
-  const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));
+  ca.items = citems.data(); ca.scratch = scratch.data(); ca.scratch_stride = (int64_t)sstride; ca.n = n;
   const bool lz4 = codec == kCodecLz4 || codec == kCodecLz4hc;
-  cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] {
-    if (ca.tile == 512) { if (lz4) k_compress<kCodecLz4, 512>(ca); else k_compress<kCodecBlosclz, 512>(ca); }
-    else { if (lz4) k_compress<kCodecLz4, 1024>(ca); else k_compress<kCodecBlosclz, 1024>(ca); }
-  });
+  ca.win_bytes = wwin; ca.p = p;
+  if (team > 1) {
+    ca.team_prime = g_team_prime < 0 ? kTeamPrime : g_team_prime;
+    const int seg = ((max_stream + team - 1) / team + kTeamTile - 1) / kTeamTile * kTeamTile;
+    ca.htab_bytes = g_team_hlog > 0 ? (2 << g_team_hlog) : hlog > 0 ? (2 << hlog) : plan_htab_bytes(std::min(max_stream, seg + ca.team_prime), clevel);
+    ca.tile = kTeamTile;
+    const size_t smem = (size_t)wwin + (size_t)team * (ca.htab_bytes + enc_work_bytes(kTeamTile)) + sizeof(TeamCtl);
+    cusim::launch(dim3(grid), dim3(32 * team), smem, [&] {
+      if (lz4) k_compress_team<kCodecLz4, kTeamTile>(ca); else k_compress_team<kCodecBlosclz, kTeamTile>(ca);
+    });
+  } else {
+    const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);
+    ca.htab_bytes = htab_bytes; ca.team_prime = 0;
+    ca.tile = enc_tile_for(max_stream);
+    const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));
+    cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] {
+      if (ca.tile == 512) { if (lz4) k_compress<kCodecLz4, 512>(ca); else k_compress<kCodecBlosclz, 512>(ca); }
+      else { if (lz4) k_compress<kCodecLz4, 1024>(ca); else k_compress<kCodecBlosclz, 1024>(ca); }
+    });
+  }
   PlaceArgs pl;
   pl.chunks = ch.data(); pl.info = info.data(); pl.items = citems.data(); pl.state = state.data(); pl.n = n;
   cusim::launch(dim3(std::min(grid, n)), dim3(256), 2 * 256 * sizeof(int32_t), [&] { k_place(pl); });
   FinalizeArgs fa;
   fa.chunks = ch.data(); fa.info = info.data(); fa.state = state.data(); fa.items = citems.data();
-  fa.scratch = scratch.data(); fa.scratch_stride = wwin; fa.res = res.data(); fa.base = base.data();
+  fa.scratch = scratch.data(); fa.scratch_stride = (int64_t)sstride; fa.res = res.data(); fa.base = base.data();
   fa.n = n; fa.total_items = (int32_t)items; fa.win_bytes = wwin; fa.p = p;
   cusim::launch(dim3(std::min<int>(grid, (int)items)), dim3(kCtaThreads), (size_t)wwin, [&] { k_finalize(fa); });
   for (int i = 0; i < n; i++) {
@@ -173,6 +190,7 @@ int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int
   return result;
 }
 
+void sim_set_team(int warps, int prime, int hlog) { g_team = warps; g_team_prime = prime; g_team_hlog = hlog; }
 unsigned long long sim_collectives() { return cusim::S().collectives; }
 int sim_last_paired() { return g_last_paired; }
 // lz4 / blosclz batched decode counters: [batches, sequences executed in batches, (unused), matches copied in stream

@@ -396,6 +396,35 @@ def test_compress_levels_decodable_by_checker(codec, clevel):
     assert sum(sizes) < 6 * 150100 * 0.9          # every level still compresses this data
 
 
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+@pytest.mark.parametrize("team,prime", [(2, 0), (3, 2048), (4, 0), (4, 2048), (8, 128), (8, 65536)])
+def test_compress_teams_decodable_by_checker(codec, team, prime):
+    """k_compress_team: the warps of a CTA encode consecutive segments of one stream and join their bodies
+    (lz_encode_warp<SEG>, lz_join_team).  Whatever the team size and the priming, the chunk is an ordinary one -- the
+    reference / the oracle and the kernel decode it -- and it stays close to what one warp per stream makes of the same data (image planes with a primed table: within 3 %; text with cold 4 KiB tables: 25 % worse)
+    makes of the same data; streams shorter than a segment, leftover blocks and run streams go through the team too."""
+    cases = [(2, "half", 150000), (2, "sensor", 98304 + 10), (1, "text", 70001), (1, "ramp", 65536), (1, "longrun", 40000),
+             (4, "f32", 131072 + 52), (1, "random", 33000), (2, "zeros", 66000), (1, "sparse", 50000), (1, "iota", 600)]
+    try:
+        for ts, kind, n in cases:
+            src = _data.make_data(kind, n, ts, seed=3)
+            for filt in (_data.SHUFFLE, _data.BITSHUFFLE) if ts == 4 else (_data.SHUFFLE,):
+                _sim.set_team(1)
+                (st0, solo), = _sim.compress_batch([src], codec, 9, ts, filt, 32768)
+                _sim.set_team(team, prime)
+                (st, chunk), = _sim.compress_batch([src], codec, 9, ts, filt, 32768)
+                assert st == 0 and st0 == 0
+                rc, back = _checker_decompress(chunk)
+                assert rc == src.size and np.array_equal(back, src), (ts, kind, filt)
+                (st2, out), = _sim.decompress_batch([chunk])
+                assert st2 == 0 and np.array_equal(out, src)
+                assert chunk.size <= solo.size * 1.35 + 128, (ts, kind, chunk.size, solo.size)
+                if kind in ("half", "sensor") and prime >= 2048:
+                    assert chunk.size <= solo.size * 1.03, (ts, kind, chunk.size, solo.size)
+    finally:
+        _sim.set_team(-1, -1)
+
+
 def test_compress_capacity_rules():
     src = _data.make_data("random", 50000, 1)
     (st, chunk), = _sim.compress_batch([src], _data.LZ4, 5, 1, _data.SHUFFLE, 32768, caps=[50000 + 31])

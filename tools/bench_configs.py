@@ -25,7 +25,9 @@ except Exception:
 
 
 def run_case(name, pieces, codec, clevel, ts, filt, reps, chunks=None):
-    """chunks given (numpy, e.g. reference zstd chunks): decode only."""
+    """chunks given (numpy, e.g. reference zstd chunks): decode only.  B2G_CASE=<substring> runs the matching cases only."""
+    if os.environ.get("B2G_CASE") and os.environ["B2G_CASE"] not in name:
+        return
     n = len(pieces)
     total = sum(int(p.size) for p in pieces)
     raw = torch.empty(total, dtype=torch.uint8)
