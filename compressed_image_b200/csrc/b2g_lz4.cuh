@@ -159,8 +159,8 @@ __device__ __forceinline__ void lz_batch_execute(const IN& I, const OUT& O, uint
     const int k = __ffs((int)rest) - 1;
     rest &= rest - 1;
     const int c = __shfl_sync(kFull, cpy, k), o = __shfl_sync(kFull, off, k), m = __shfl_sync(kFull, ml, k);
-    if (o == 0) fill_bytes(out + c, 0, m, lane, 32);
-    else lz_match_copy(out, c, o, m, lane);
+    if (o == 0) warp_fill(O, c, 0u, m, lane);
+    else warp_match_copy(O, c, o, m, lane);
     __syncwarp();
   }
 }
@@ -296,8 +296,8 @@ __device__ __forceinline__ int lz4_decode_warp_t(const uint8_t* in, int n, uint8
     if (mend > cap - 5) return -1;  // lz4.c:2419-2423: the last 5 bytes are always literals
     if (INPLACE && mend > a + ipn) return -2;
     __syncwarp();                   // literals (and every earlier match) visible before the match is read
-    if (offset == 0) fill_bytes(out + cpy, 0, ml, lane, 32);
-    else lz_match_copy(out, cpy, (int)offset, ml, lane);
+    if (offset == 0) warp_fill(O, cpy, 0u, ml, lane);
+    else warp_match_copy(O, cpy, (int)offset, ml, lane);
     __syncwarp();
     op = mend;
     ip = ipn;

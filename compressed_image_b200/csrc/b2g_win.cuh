@@ -126,4 +126,49 @@ __device__ __forceinline__ void warp_copy(const IN& I, int s, const OUT& O, int 
   if (lane < t) O.st8(d + 4 * nw + lane, I.ld8(s + 4 * nw + lane));
 }
 
+// O[d .. d+n) = value, by one warp (uniform arguments): head bytes up to a word boundary, words, tail bytes.
+template <class OUT>
+__device__ __forceinline__ void warp_fill(const OUT& O, int d, uint32_t value, int n, int lane) {
+  const int h = min((int)((4u - O.low2(d)) & 3u), n);
+  if (lane < h) O.st8(d + lane, value);
+  d += h; n -= h;
+  const int nw = n >> 2;
+  const uint32_t w = 0x01010101u * (value & 0xffu);
+  for (int i = lane; i < nw; i += 32) O.st32(d + 4 * i, w);
+  const int t = n & 3;
+  if (lane < t) O.st8(d + 4 * nw + lane, value);
+}
+
+// LZ77 back-reference by one warp through a view: O[op .. op+len) = O[op-dist ..) with byte-serial (overlapping)
+// semantics, dist >= 1 (lz_match_copy of b2g_copy.cuh for a window behind a view: in a shared-memory window every
+// access is an ld.shared / st.shared instead of a generic load / store).  The caller has made earlier writes visible.
+template <class OUT>
+__device__ __forceinline__ void warp_match_copy(const OUT& O, int op, int dist, int len, int lane) {
+  const int match = op - dist;
+  if (dist >= len) {
+    if (len >= 64) {
+      // word-granular; the 4-byte slack warp_copy reads past the source's end lies in [op, op + 8): written by this very
+      // copy, never used (the funnel shift only keeps source bytes)
+      warp_copy(O, match, O, op, len, lane);
+    } else {
+      for (int i = lane; i < len; i += 32) O.st8(op + i, O.ld8(match + i));
+    }
+  } else if (dist == 1) {
+    warp_fill(O, op, O.ld8(match), len, lane);
+  } else if (dist >= 32) {
+    for (int i = 0; i < len; i += 32) {  // each 32-byte step only reads bytes finished by earlier steps
+      if (i + lane < len) O.st8(op + i + lane, O.ld8(match + i + lane));
+      __syncwarp();
+    }
+  } else {  // short period: replicate the `dist` bytes before op
+    int r = lane % dist;
+    const int step = 32 % dist;
+    for (int i = lane; i < len; i += 32) {
+      O.st8(op + i, O.ld8(match + r));
+      r += step;
+      if (r >= dist) r -= dist;
+    }
+  }
+}
+
 }  // namespace b2g
