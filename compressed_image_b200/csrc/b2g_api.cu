@@ -184,6 +184,7 @@ struct CompGeom {
 // B2G_TEAM_PRIME = positions primed in front of a segment; B2G_TEAM_HLOG = log2 of the per-warp table entries.
 static const int g_team_env = [] { const char* e = getenv("B2G_TEAM"); return e ? atoi(e) : -1; }();
 static const int g_team_prime_env = [] { const char* e = getenv("B2G_TEAM_PRIME"); return e ? atoi(e) : -1; }();
+static const int g_team_sparse_env = [] { const char* e = getenv("B2G_TEAM_SPARSE"); return e ? atoi(e) : -1; }();
 static const int g_team_hlog_env = [] { const char* e = getenv("B2G_TEAM_HLOG"); return e ? atoi(e) : 0; }();
 
 int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
@@ -456,6 +457,7 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.htab_bytes = g.htab;
   ca.tile = g.tile;
   ca.team_prime = g.prime;
+  ca.team_prime_step = g_team_sparse_env < 0 ? plan_team_prime_step(max_stream) : (g_team_sparse_env ? 4 : 1);
   ca.p = cp;
   const int cgrid = (int)std::min<int64_t>(g.grid, g.team > 1 ? items : (items + g.warps - 1) / g.warps);
   {

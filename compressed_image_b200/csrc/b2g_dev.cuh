@@ -24,7 +24,8 @@ constexpr int kCtaWarps = kCtaThreads / 32;
 // many positions in front of its segment a warp's hash table is primed with.  Measured on 32 KiB streams (cfg 1: LZ4
 // on unsplit uint8 blocks; cfg 3: blosclz on bit-shuffled blocks): four warps x 8 KiB primed with the 8 KiB in front
 // compress 2.07x / 1.47x faster than one warp per stream at -0.3 % / +0.3 % ratio; 4 KiB segments or less priming
-// are faster still but cost 2-4 % ratio.  On 16 KiB streams two warps gain nothing and four cost 0.55 % ratio for 8 %.
+// are faster still but cost 2-4 % ratio.  On 16 KiB streams four warps cost 0.55 % ratio for 8 %; two warps gain 5 % at
+// -0.08 % when the second one primes its table with every fourth position only (plan_team_prime_step).
 constexpr int kTeamSegment = 8192;
 constexpr int kTeamMaxWarps = 8;
 constexpr int kTeamTile = 512;

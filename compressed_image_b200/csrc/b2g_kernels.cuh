@@ -654,6 +654,7 @@ struct CompressArgs {
                                  // htab_bytes + enc_work_bytes(tile), see enc_work()
   int32_t tile;                  // encoder tile (positions), enc_tile_for(largest stream of the batch)
   int32_t team_prime;            // k_compress_team: positions in front of a segment that prime its hash table
+  int32_t team_prime_step;       // 1 = every one of them, 4 = every fourth
   CParams p;
 };
 
@@ -846,7 +847,7 @@ __global__ void __launch_bounds__(256, 2) k_compress_team(CompressArgs a) {
         const int bstride = team_body_stride(seglen);
         if (sb < n) {
           lz_encode_warp<CODEC, TILE, true>(win, n, bodies + (size_t)warp * (size_t)bstride, bstride, ew, sb, se, a.team_prime,
-                                            &tc->seg[warp]);
+                                            &tc->seg[warp], a.team_prime_step);
         } else if (lane == 0) {
           tc->seg[warp].p0 = -1;
           tc->seg[warp].bytes = 0;

@@ -140,7 +140,8 @@ struct EncSeg {
 // loses its literal run, there is no closing run.  Returns the body bytes, -1 when they do not fit in cap.
 template <int CODEC, int TILE, bool SEG = false>
 __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t* out, int cap, const EncWork& w,
-                                              int seg_begin = 0, int seg_end = 0, int prime = 0, EncSeg* seg = nullptr) {
+                                              int seg_begin = 0, int seg_end = 0, int prime = 0, EncSeg* seg = nullptr,
+                                              int prime_step = 1) {
   constexpr bool LZ4 = CODEC == kCodecLz4;
   const int lane = lane_id();
   const EncIn I(in);
@@ -161,15 +162,25 @@ __device__ __forceinline__ int lz_encode_warp(const uint8_t* in, int n, uint8_t*
   }
   for (int i = lane; i < (1 << w.hlog); i += 32) w.htab[i] = 0;
   __syncwarp();
-  if (SEG) {  // positions in front of the segment: inserted, never probed (whichever lane wins a slot is a valid candidate)
-    for (int pb = max(0, seg_begin - prime); pb < seg_begin; pb += 128) {
-      const int wb = pb + 4 * (lane >> 2);
-      const unsigned sh = (unsigned)(lane & 3) * 8u;
+  if (SEG && prime > 0) {  // positions in front of the segment: inserted, never probed (whichever lane wins a slot is a
+                           // valid candidate).  prime_step 4: every fourth position only -- a quarter of the work; a match
+                           // whose source starts between two of them is found up to three bytes late and grown backwards
+    if (prime_step == 4) {
+      for (int pb = max(0, seg_begin - prime); pb < seg_begin; pb += 128) {
+        const uint32_t s4 = I.ld32(pb + 4 * lane);
+        w.htab[(s4 * 2654435761u) >> (32 - w.hlog)] = (uint16_t)(pb + 4 * lane);
+        __syncwarp();
+      }
+    } else {
+      for (int pb = max(0, seg_begin - prime); pb < seg_begin; pb += 128) {
+        const int wb = pb + 4 * (lane >> 2);
+        const unsigned sh = (unsigned)(lane & 3) * 8u;
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const uint32_t s4 = __funnelshift_r(I.ld32(wb + 32 * j), I.ld32(wb + 32 * j + 4), sh);
-        w.htab[(s4 * 2654435761u) >> (32 - w.hlog)] = (uint16_t)(pb + 32 * j + lane);
-        __syncwarp();  // later groups overwrite earlier ones
+        for (int j = 0; j < 4; j++) {
+          const uint32_t s4 = __funnelshift_r(I.ld32(wb + 32 * j), I.ld32(wb + 32 * j + 4), sh);
+          w.htab[(s4 * 2654435761u) >> (32 - w.hlog)] = (uint16_t)(pb + 32 * j + lane);
+          __syncwarp();  // later groups overwrite earlier ones
+        }
       }
     }
   }

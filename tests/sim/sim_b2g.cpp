@@ -13,7 +13,7 @@ static size_t au(size_t v, size_t a) { return (v + a - 1) / a * a; }
 static int g_last_paired = 0;
 // encoder teams: -1 = as the host library decides (plan_team_warps), 0 / 1 = k_compress (one warp per stream), S > 1 =
 // k_compress_team with S warps; prime < 0 = kTeamPrime
-static int g_team = -1, g_team_prime = -1, g_team_hlog = 0;
+static int g_team = -1, g_team_prime = -1, g_team_hlog = 0, g_team_sparse = -1;
 
 extern "C" {
 
@@ -112,8 +112,8 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   ca.win_bytes = wwin; ca.p = p;
   if (team > 1) {
     ca.team_prime = g_team_prime < 0 ? kTeamPrime : g_team_prime;
-    const int seg = ((max_stream + team - 1) / team + kTeamTile - 1) / kTeamTile * kTeamTile;
-    ca.htab_bytes = g_team_hlog > 0 ? (2 << g_team_hlog) : hlog > 0 ? (2 << hlog) : plan_htab_bytes(std::min(max_stream, seg + ca.team_prime), clevel);
+    ca.team_prime_step = g_team_sparse < 0 ? plan_team_prime_step(max_stream) : (g_team_sparse ? 4 : 1);
+    ca.htab_bytes = g_team_hlog > 0 ? (2 << g_team_hlog) : hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);  // as b2g_api.cu
     ca.tile = kTeamTile;
     const size_t smem = (size_t)wwin + (size_t)team * (ca.htab_bytes + enc_work_bytes(kTeamTile)) + sizeof(TeamCtl);
     cusim::launch(dim3(grid), dim3(32 * team), smem, [&] {
@@ -121,7 +121,7 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
     });
   } else {
     const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);
-    ca.htab_bytes = htab_bytes; ca.team_prime = 0;
+    ca.htab_bytes = htab_bytes; ca.team_prime = 0; ca.team_prime_step = 1;
     ca.tile = enc_tile_for(max_stream);
     const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));
     cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] {
@@ -191,6 +191,7 @@ int sim_stream_encode(int codec, const void* src, int n, void* dst, int cap, int
 }
 
 void sim_set_team(int warps, int prime, int hlog) { g_team = warps; g_team_prime = prime; g_team_hlog = hlog; }
+void sim_set_team_sparse(int sparse) { g_team_sparse = sparse; }
 unsigned long long sim_collectives() { return cusim::S().collectives; }
 int sim_last_paired() { return g_last_paired; }
 // lz4 / blosclz batched decode counters: [batches, sequences executed in batches, (unused), matches copied in stream
