@@ -89,13 +89,17 @@ def compress_batch(srcs, codec, clevel, typesize, filt, blocksize, caps=None, wi
     return res
 
 
-def set_team(warps=-1, prime=-1, hlog=0):
+def set_team(warps=-1, prime=-1, hlog=0, sparse=-1):
     """Encoder teams in sim_compress_batch: warps -1 = as the library decides (plan_team_warps), 0 / 1 = one warp per
-    stream (k_compress), N > 1 = k_compress_team with N warps; prime -1 = the library's default."""
+    stream (k_compress), N > 1 = k_compress_team with N warps; prime -1 = the library's default; sparse 1 / 0 = prime with
+    every fourth position / every position, -1 = as the library decides (plan_team_prime_step)."""
     L = lib()
     L.sim_set_team.argtypes = [C.c_int] * 3
     L.sim_set_team.restype = None
     L.sim_set_team(warps, prime, hlog)
+    L.sim_set_team_sparse.argtypes = [C.c_int]
+    L.sim_set_team_sparse.restype = None
+    L.sim_set_team_sparse(sparse)
 
 
 def run_filter(filt, forward, typesize, src, blocksize, version=5, grid=2):

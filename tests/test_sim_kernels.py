@@ -397,8 +397,9 @@ def test_compress_levels_decodable_by_checker(codec, clevel):
 
 
 @pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
-@pytest.mark.parametrize("team,prime", [(2, 0), (3, 2048), (4, 0), (4, 2048), (8, 128), (8, 65536)])
-def test_compress_teams_decodable_by_checker(codec, team, prime):
+@pytest.mark.parametrize("team,prime,sparse", [(2, 0, 0), (2, 8192, 1), (3, 2048, 0), (4, 0, 0), (4, 2048, 0), (4, 8192, 1),
+                                               (8, 128, 0), (8, 65536, 0)])
+def test_compress_teams_decodable_by_checker(codec, team, prime, sparse):
     """k_compress_team: the warps of a CTA encode consecutive segments of one stream and join their bodies
     (lz_encode_warp<SEG>, lz_join_team).  Whatever the team size and the priming, the chunk is an ordinary one -- the
     reference / the oracle and the kernel decode it -- and it stays close to what one warp per stream makes of the same data (image planes with a primed table: within 3 %; text with cold 4 KiB tables: 25 % worse)
@@ -411,7 +412,7 @@ def test_compress_teams_decodable_by_checker(codec, team, prime):
             for filt in (_data.SHUFFLE, _data.BITSHUFFLE) if ts == 4 else (_data.SHUFFLE,):
                 _sim.set_team(1)
                 (st0, solo), = _sim.compress_batch([src], codec, 9, ts, filt, 32768)
-                _sim.set_team(team, prime)
+                _sim.set_team(team, prime, sparse=sparse)
                 (st, chunk), = _sim.compress_batch([src], codec, 9, ts, filt, 32768)
                 assert st == 0 and st0 == 0
                 rc, back = _checker_decompress(chunk)
