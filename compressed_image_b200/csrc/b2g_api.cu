@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <climits>
 #include <condition_variable>
 #include <functional>
@@ -792,10 +793,23 @@ static void drain_lanes(b2g_ctx* c) {
   if (c->d2h_stream) cudaStreamSynchronize(c->d2h_stream);
 }
 
+// B2G_TRACE=1 (diagnosis): when each sub-batch of a pinned host-pointer batch completed on the device and when the host
+// enqueued / collected it, in ms since the first traced call of the process, on stderr (DESIGN.md section 3 reads one).
+static const bool g_trace = [] { const char* e = getenv("B2G_TRACE"); return e && e[0] == '1'; }();
+static cudaEvent_t g_trace_origin = nullptr;
+static std::chrono::steady_clock::time_point g_trace_host0;
+static double trace_host_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_trace_host0).count(); }
+
 static int ensure_sub_events(b2g_ctx* c, int nsub) {
+  if (g_trace && !g_trace_origin) {
+    CU(cudaEventCreate(&g_trace_origin));
+    CU(cudaEventRecord(g_trace_origin, c->lanes[0].stream));
+    CU(cudaEventSynchronize(g_trace_origin));
+    g_trace_host0 = std::chrono::steady_clock::now();
+  }
   while ((int)c->sub_done.size() < nsub) {
     cudaEvent_t e = nullptr;
-    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e, g_trace ? cudaEventDefault : cudaEventDisableTiming));
     c->sub_done.push_back(e);
   }
   if (!c->d2h_stream) CU(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
@@ -1090,7 +1104,9 @@ int b2g_decompress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_
   }
   return 0;
   };
+  const double trace_t0 = g_trace ? trace_host_ms() : 0;
   if (int rc = enqueue_all()) { drain_lanes(c); return rc; }
+  if (g_trace) fprintf(stderr, "b2g-trace ctx=%p enqueue host=%.3f .. %.3f (%d sub-batches)\n", (void*)c, trace_t0, trace_host_ms(), nsub);
   c->pend = chunks; c->pend_n = n; c->pend_kind = 1;
   return 0;
 }
@@ -1243,7 +1259,9 @@ int b2g_compress_batch_async(b2g_ctx* c, b2g_chunk* chunks, int n, void* cuda_st
   }
   return 0;
   };
+  const double trace_t0 = g_trace ? trace_host_ms() : 0;
   if (int rc = enqueue_all()) { drain_lanes(c); return rc; }
+  if (g_trace) fprintf(stderr, "b2g-trace ctx=%p enqueue host=%.3f .. %.3f (%d sub-batches)\n", (void*)c, trace_t0, trace_host_ms(), nsub);
   c->pend = chunks; c->pend_n = n; c->pend_kind = 2;
   return 0;
 }
@@ -1259,8 +1277,14 @@ static int wait_host_batch(b2g_ctx* c) {
   const int nsub = (int)c->pend_bounds.size() - 1;
   const DResult* r = (const DResult*)c->h_res_all.p;
   int rc_all = 0;
+  if (g_trace) fprintf(stderr, "b2g-trace ctx=%p kind=%d wait begins host=%.3f\n", (void*)c, kind, trace_host_ms());
   for (int k = 0; k < nsub; k++) {
     if (cuda_fail(cudaEventSynchronize(c->sub_done[k]), "cudaEventSynchronize")) { rc_all = B2G_ERR_NO_DEVICE; break; }
+    if (g_trace) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, g_trace_origin, c->sub_done[k]);
+      fprintf(stderr, "b2g-trace ctx=%p kind=%d sub=%d done_dev=%.3f seen_host=%.3f\n", (void*)c, kind, k, ms, trace_host_ms());
+    }
     for (int q = c->pend_bounds[k]; q < c->pend_bounds[k + 1]; q++) {
       const int i = c->pend_order[q];
       chunks[i].status = r[q].status;
@@ -1273,6 +1297,7 @@ static int wait_host_batch(b2g_ctx* c) {
   }
   for (Lane& L : c->lanes) if (cuda_fail(cudaStreamSynchronize(L.stream), "cudaStreamSynchronize")) rc_all = B2G_ERR_NO_DEVICE;
   if (c->d2h_stream && cuda_fail(cudaStreamSynchronize(c->d2h_stream), "cudaStreamSynchronize")) rc_all = B2G_ERR_NO_DEVICE;
+  if (g_trace) fprintf(stderr, "b2g-trace ctx=%p kind=%d wait ends host=%.3f\n", (void*)c, kind, trace_host_ms());
   return rc_all;
 }
 

@@ -29,3 +29,16 @@ def chunks(h2d, d2h, reps=3, sz=4 << 20):
     return n / dt / 1e9
 print("4 MiB pieces, both: %.1f GB/s per direction" % chunks(True, True))
 print("1.6 MiB pieces D2H: %.1f GB/s" % chunks(False, True, sz=1600000))
+# the e2e step's pattern: 4 MiB pieces in both directions, spread over several streams each way
+def multi(nstreams, reps=3, sz=4 << 20, sz2=None):
+    ss = [torch.cuda.Stream() for _ in range(2 * nstreams)]
+    torch.cuda.synchronize(); t = time.perf_counter()
+    for _ in range(reps):
+        for k, o in enumerate(range(0, n, sz)):
+            with torch.cuda.stream(ss[k % nstreams]): d1[o:o+sz].copy_(h1[o:o+sz], non_blocking=True)
+            with torch.cuda.stream(ss[nstreams + k % nstreams]): h2[o:o+sz].copy_(d2[o:o+sz], non_blocking=True)
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t) / reps
+    return n / dt / 1e9
+for ns in (1, 2, 6, 12):
+    print("4 MiB pieces, both directions, %d streams each way: %.1f GB/s per direction" % (ns, multi(ns)))
+print("32 MiB pieces, both directions, 6 streams each way: %.1f GB/s per direction" % multi(6, sz=32 << 20))
