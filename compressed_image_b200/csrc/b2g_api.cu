@@ -1278,8 +1278,31 @@ static int wait_host_batch(b2g_ctx* c) {
   const DResult* r = (const DResult*)c->h_res_all.p;
   int rc_all = 0;
   if (g_trace) fprintf(stderr, "b2g-trace ctx=%p kind=%d wait begins host=%.3f\n", (void*)c, kind, trace_host_ms());
-  for (int k = 0; k < nsub; k++) {
-    if (cuda_fail(cudaEventSynchronize(c->sub_done[k]), "cudaEventSynchronize")) { rc_all = B2G_ERR_NO_DEVICE; break; }
+  // Sub-batches finish in whatever order the copy engines served their lanes (traced: 0, 4, 2, 6, 1, 5, 3, 7).  A compress
+  // batch is collected in COMPLETION order, so that a sub-batch's chunk copies are issued when its sizes arrive and not
+  // when every earlier-numbered one has arrived too; a decompress batch has nothing to issue and is read in order.
+  std::vector<char> seen((size_t)nsub, 0);
+  for (int done = 0; done < nsub; done++) {
+    int k = -1;
+    if (kind == 2) {
+      for (;;) {
+        bool failed = false;
+        for (int j = 0; j < nsub && k < 0; j++) {
+          if (seen[(size_t)j]) continue;
+          const cudaError_t q = cudaEventQuery(c->sub_done[j]);
+          if (q == cudaSuccess) k = j;
+          else if (q != cudaErrorNotReady) { failed = cuda_fail(q, "cudaEventQuery"); k = j; }
+        }
+        if (failed) rc_all = B2G_ERR_NO_DEVICE;
+        if (k >= 0) break;
+        std::this_thread::yield();
+      }
+      if (rc_all) break;
+    } else {
+      k = done;
+      if (cuda_fail(cudaEventSynchronize(c->sub_done[k]), "cudaEventSynchronize")) { rc_all = B2G_ERR_NO_DEVICE; break; }
+    }
+    seen[(size_t)k] = 1;
     if (g_trace) {
       float ms = 0;
       cudaEventElapsedTime(&ms, g_trace_origin, c->sub_done[k]);
