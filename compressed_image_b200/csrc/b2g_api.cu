@@ -198,9 +198,12 @@ int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
     g.prime = g_team_prime_env < 0 ? kTeamPrime : (g_team_prime_env + 127) / 128 * 128;
     g.tile = kTeamTile;
     g.htab = g_team_hlog_env > 0 ? (2 << std::min(std::max(g_team_hlog_env, 6), 12)) : plan_htab_bytes(max_stream, c->p.clevel);
+    const size_t per_warp = (size_t)g.htab + (size_t)enc_work_bytes(g.tile);
+    while (g.team > 1 && (size_t)g.win + (size_t)g.team * per_warp + sizeof(TeamCtl) > 227 * 1024) g.team--;  // very large streams
+  }
+  if (g.team > 1) {
     g.warps = g.team;
     g.smem = (size_t)g.win + (size_t)g.team * ((size_t)g.htab + (size_t)enc_work_bytes(g.tile)) + sizeof(TeamCtl);
-    if (g.smem > 227 * 1024) return B2G_ERR_BLOCKSIZE;
     g.scratch_stride = (size_t)plan_team_scratch_stride(g.win);
     g.which = lz4codec ? 4 : 5;
     g.fn = lz4codec ? (const void*)k_compress_team<kCodecLz4, kTeamTile> : (const void*)k_compress_team<kCodecBlosclz, kTeamTile>;

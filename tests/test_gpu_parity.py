@@ -214,6 +214,23 @@ def test_compress_batch_lookback_many_ctas():
         assert st == 0 and np.array_equal(out, s)
 
 
+@pytest.mark.parametrize("codec", [_data.LZ4, _data.BLOSCLZ])
+@pytest.mark.parametrize("ts,bs", [(1, 65536), (1, 131072), (1, 163840), (1, 196608), (2, 65536), (4, 262144), (2, 24576)])
+def test_compress_stream_sizes_across_the_team_geometries(codec, ts, bs):
+    """Streams from 12 KiB to 192 KiB (the encoder's limit): one warp per stream, teams of 2 ... 8 warps, and the sizes
+    where the shared window leaves room for fewer warps than a segment every 8 KiB asks for.  Every chunk is decoded by
+    the reference / the oracle and by the kernel."""
+    g = _gpu()
+    srcs = [_data.make_data(k, 3 * bs + 1000 * i + 77, ts, seed=5 + i) for i, k in enumerate(("half", "text", "sparse", "ramp"))]
+    res = g.compress_batch(srcs, codec, 9, ts, _data.SHUFFLE, bs)
+    for s, (st, chunk) in zip(srcs, res):
+        assert st == 0 and 0 < chunk.size <= s.size + 32
+        rc, back = _checker_decompress(chunk)
+        assert rc == s.size and np.array_equal(back, s), (ts, bs)
+    for s, (st, out) in zip(srcs, g.decompress_batch([c for _, c in res])):
+        assert st == 0 and np.array_equal(out, s)
+
+
 def test_compress_capacity_rules():
     g = _gpu()
     src = _data.make_data("random", 50000, 1)
