@@ -88,7 +88,7 @@ struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // [0] descriptors uploaded, [1] plan done, [2] kernels done
   cudaEvent_t res_ready = nullptr;                   // per-chunk results landed in h_res
-  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_stage, d_pair;
+  DevBuf d_chunks, d_info, d_res, d_base, d_ctl, d_cinfo, d_state, d_items, d_scratch, d_slab, d_stage, d_pair, d_team;
   HostBuf h_chunks, h_res, h_cinfo, h_base;
   HostBuf h_in, h_out;                               // pinned bounce buffers of the staged (pageable-caller) path
   cudaEvent_t piece[kStagePieces] = {};              // D2H pieces of a staged sub-batch landed in h_out
@@ -96,7 +96,7 @@ struct Lane {
   int st_npieces = 0, st_per = 1;
   std::vector<size_t> st_loc;
   void release() {
-    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_stage, &d_pair}) b->release();
+    for (DevBuf* b : {&d_chunks, &d_info, &d_res, &d_base, &d_ctl, &d_cinfo, &d_state, &d_items, &d_scratch, &d_slab, &d_stage, &d_pair, &d_team}) b->release();
     for (HostBuf* b : {&h_chunks, &h_res, &h_cinfo, &h_base, &h_in, &h_out}) b->release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : piece) if (e) cudaEventDestroy(e);
@@ -204,7 +204,6 @@ int compress_geometry(b2g_ctx* c, int max_stream, CompGeom& g) {
   if (g.team > 1) {
     g.warps = g.team;
     g.smem = (size_t)g.win + (size_t)g.team * ((size_t)g.htab + (size_t)enc_work_bytes(g.tile)) + sizeof(TeamCtl);
-    g.scratch_stride = (size_t)plan_team_scratch_stride(g.win);
     g.which = lz4codec ? 4 : 5;
     g.fn = lz4codec ? (const void*)k_compress_team<kCodecLz4, kTeamTile> : (const void*)k_compress_team<kCodecBlosclz, kTeamTile>;
     if (int rc = raise_smem_limit(c->dev, 8 + g.which, g.fn, g.smem)) return rc;   // slots 12, 13
@@ -464,6 +463,13 @@ int enqueue_compress(b2g_ctx* c, Lane& L, const DChunk* h_desc, const int32_t* n
   ca.team_prime_step = g_team_sparse_env < 0 ? plan_team_prime_step(max_stream) : (g_team_sparse_env ? 4 : 1);
   ca.p = cp;
   const int cgrid = (int)std::min<int64_t>(g.grid, g.team > 1 ? items : (items + g.warps - 1) / g.warps);
+  ca.team_bodies = nullptr;
+  ca.team_body_bytes = 0;
+  if (g.team > 1) {
+    ca.team_body_bytes = (int64_t)plan_team_body_bytes(g.win);
+    if (int rc = L.d_team.ensure((size_t)ca.team_body_bytes * (size_t)std::max(cgrid, 1) + 256)) return rc;
+    ca.team_bodies = (uint8_t*)L.d_team.p;
+  }
   {
     void* kargs[] = {(void*)&ca};
     CU(cudaLaunchKernel(g.fn, dim3((unsigned)cgrid), dim3((unsigned)(32 * g.warps)), kargs, g.smem, s));

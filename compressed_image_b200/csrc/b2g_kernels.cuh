@@ -655,6 +655,8 @@ struct CompressArgs {
   int32_t tile;                  // encoder tile (positions), enc_tile_for(largest stream of the batch)
   int32_t team_prime;            // k_compress_team: positions in front of a segment that prime its hash table
   int32_t team_prime_step;       // 1 = every one of them, 4 = every fourth
+  uint8_t* team_bodies;          // k_compress_team: [gridDim.x][team_body_bytes] the segment bodies of the item a CTA is on
+  int64_t team_body_bytes;
   CParams p;
 };
 
@@ -789,7 +791,8 @@ __global__ void __launch_bounds__(256, 2) k_compress(CompressArgs a) {
 // instead of as many as 227 KiB / (window + table) -- the encoder is a latency-bound dependent chain, more resident
 // warps are what it lacks.  Costs: a match may not cross a segment boundary, and a segment's table only knows the
 // team_prime positions in front of it (ratio: see DESIGN.md); every item costs five CTA barriers.
-// Scratch slot of an item: [win_bytes joined stream][S bodies of team_body_stride(segment) bytes].
+// The bodies live in a per-CTA area (they are dead once the item is joined: a few MB for the whole grid, L2-resident);
+// the item's scratch slot receives the joined stream, as in k_compress.
 struct TeamCtl {
   EncSeg seg[kTeamMaxWarps];
   int32_t item;
@@ -843,7 +846,7 @@ __global__ void __launch_bounds__(256, 2) k_compress_team(CompressArgs a) {
         hlog = hlog < 6 ? 6 : (hlog > hmax ? hmax : hlog);
         const EncWork ew = enc_work(work, a.htab_bytes, hlog, TILE, CODEC == kCodecBlosclz || a.p.clevel > 5 ? 4 : (a.p.clevel > 2 ? 5 : 6));
         uint8_t* out = a.scratch + (size_t)item * (size_t)a.scratch_stride;
-        uint8_t* bodies = out + a.win_bytes;
+        uint8_t* bodies = a.team_bodies + (size_t)blockIdx.x * (size_t)a.team_body_bytes;  // this CTA's, item after item
         const int bstride = team_body_stride(seglen);
         if (sb < n) {
           lz_encode_warp<CODEC, TILE, true>(win, n, bodies + (size_t)warp * (size_t)bstride, bstride, ew, sb, se, a.team_prime,

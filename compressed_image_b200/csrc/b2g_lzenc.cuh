@@ -487,15 +487,6 @@ __device__ __forceinline__ int lz_join_team(const uint8_t* in, int n, const EncS
     }
     const uint8_t* body = bodies + (size_t)warp * (size_t)body_stride;
     copy_bytes(out + q, body, segs[warp].bytes, lane, 32);
-#ifndef B2G_SIM
-    // The body has been read for the last time: the 128-byte lines that hold nothing else are dropped from L2 instead of
-    // being written back to HBM when they age out (measured: 129 MB of DRAM writes per launch against 80 MB for what the
-    // kernel has to keep).
-    __syncwarp();
-    const uintptr_t lo = ((uintptr_t)body + 127) & ~(uintptr_t)127, hi = ((uintptr_t)body + (uintptr_t)segs[warp].bytes) & ~(uintptr_t)127;
-    for (uintptr_t a = lo + (uintptr_t)lane * 128; a + 128 <= hi; a += 32 * 128)
-      asm volatile("discard.global.L2 [%0], 128;" ::"l"(a) : "memory");
-#endif
   }
   if (warp == S - 1) {
     if (LZ4) {

@@ -81,8 +81,8 @@ inline int plan_htab_bytes(int neblock, int clevel = 9) {
 // Encoder teams (k_compress_team): streams above one segment are encoded by several warps of one CTA side by side, each
 // warp a segment of the stream in the CTA's one shared-memory window.  Warps per team for a batch whose largest stream
 // is `max_stream` bytes (1 = every warp its own stream, k_compress), the segment of a `neblock`-byte stream (a multiple
-// of the encoder tile), the positions in front of a segment its hash table is primed with, and the scratch slot of one
-// stream item: the joined stream (< win bytes) followed by the segments' bodies (segment + 64 bytes each).
+// of the encoder tile), the positions in front of a segment its hash table is primed with, and the per-CTA area that
+// holds the segments' bodies (segment + 64 bytes each) of the item the CTA is working on.
 inline int plan_team_warps(int max_stream) {
   if (max_stream <= kTeamSegment) return 1;
   return std::min(kTeamMaxWarps, (max_stream + kTeamSegment - 1) / kTeamSegment);
@@ -90,6 +90,6 @@ inline int plan_team_warps(int max_stream) {
 // Two-warp teams (16 KiB planes) prime with every fourth position only: there the full insert costs as much as the
 // second warp gains (measured: 1.60 ms against 1.59 ms with one warp per stream; 1.51 ms primed sparsely, ratio -0.08 %).
 inline int plan_team_prime_step(int max_stream) { return max_stream <= 2 * kTeamSegment ? 4 : 1; }
-inline int plan_team_scratch_stride(int win) { return 2 * win + kTeamMaxWarps * (kTeamTile + 64); }
+inline int plan_team_body_bytes(int win) { return win + kTeamMaxWarps * (kTeamTile + 64); }   // per CTA
 
 }  // namespace b2g

@@ -102,7 +102,8 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   const int warps = 2;  // independent workers per simulated CTA
   const int wwin = std::max((int)au(max_stream, 16), 1024);
   const int team = g_team < 0 ? plan_team_warps(max_stream) : std::min(g_team, (int)kTeamMaxWarps);
-  const size_t sstride = team > 1 ? (size_t)plan_team_scratch_stride(wwin) : (size_t)wwin;
+  const size_t sstride = (size_t)wwin;
+  std::vector<uint8_t> team_bodies(team > 1 ? (size_t)plan_team_body_bytes(wwin) * (size_t)grid + 256 : 1);
   std::vector<CItem> citems(items + 1);
   std::vector<uint8_t> scratch(sstride * items + 256);
   CompressArgs ca;
@@ -111,6 +112,7 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
   const bool lz4 = codec == kCodecLz4 || codec == kCodecLz4hc;
   ca.win_bytes = wwin; ca.p = p;
   if (team > 1) {
+    ca.team_bodies = team_bodies.data(); ca.team_body_bytes = plan_team_body_bytes(wwin);
     ca.team_prime = g_team_prime < 0 ? kTeamPrime : g_team_prime;
     ca.team_prime_step = g_team_sparse < 0 ? plan_team_prime_step(max_stream) : (g_team_sparse ? 4 : 1);
     ca.htab_bytes = g_team_hlog > 0 ? (2 << g_team_hlog) : hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);  // as b2g_api.cu
@@ -121,7 +123,7 @@ int sim_compress_batch(int codec, int clevel, int typesize, int filter, int bloc
     });
   } else {
     const int htab_bytes = hlog > 0 ? (2 << hlog) : plan_htab_bytes(max_stream, clevel);
-    ca.htab_bytes = htab_bytes; ca.team_prime = 0; ca.team_prime_step = 1;
+    ca.htab_bytes = htab_bytes; ca.team_prime = 0; ca.team_prime_step = 1; ca.team_bodies = nullptr; ca.team_body_bytes = 0;
     ca.tile = enc_tile_for(max_stream);
     const size_t smem = (size_t)warps * ((size_t)wwin + htab_bytes + enc_work_bytes(ca.tile));
     cusim::launch(dim3(grid), dim3(32 * warps), smem, [&] {
