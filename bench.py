@@ -905,7 +905,7 @@ def run_b2g(args, rank, world, local_rank):
         a = alg_bytes / (t * 1e-3) / 1e9 if t > 0 else 0.0
         tr = traffic_j.get(name)
         launched = {"k_decode": "k_plan_decode + k_decode<false>",
-                    "k_compress": "k_compress_team<lz4, 512> (two-warp teams on the 16 KiB planes) + k_place + k_finalize"}
+                    "k_compress": "k_compress_team<lz4, 256> (two-warp teams on the 16 KiB planes) + k_place + k_finalize"}
         return {"kernel": name, "launched_as": launched.get(name), "bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s",
                 "frac": a / peak,
                 "traffic": (tr["dram_bytes_read"] + tr["dram_bytes_write"]) if tr else None,

@@ -28,7 +28,7 @@ constexpr int kCtaWarps = kCtaThreads / 32;
 // -0.08 % when the second one primes its table with every fourth position only (plan_team_prime_step).
 constexpr int kTeamSegment = 8192;
 constexpr int kTeamMaxWarps = 8;
-constexpr int kTeamTile = 512;
+constexpr int kTeamTile = 256;   // 512 leaves room for 14 warps per SM on 16 KiB planes, 256 for 16: k_compress 1.50 -> 1.43 ms
 constexpr int kTeamPrime = 8192;
 constexpr unsigned kFull = 0xffffffffu;
 

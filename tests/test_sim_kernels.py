@@ -419,7 +419,8 @@ def test_compress_teams_decodable_by_checker(codec, team, prime, sparse):
                 assert rc == src.size and np.array_equal(back, src), (ts, kind, filt)
                 (st2, out), = _sim.decompress_batch([chunk])
                 assert st2 == 0 and np.array_equal(out, src)
-                assert chunk.size <= solo.size * 1.35 + 128, (ts, kind, chunk.size, solo.size)
+                if n >= 8192:      # (a 600-byte stream forced through a team is cut every 256 bytes: nothing to compare)
+                    assert chunk.size <= solo.size * 1.35 + 128, (ts, kind, chunk.size, solo.size)
                 if kind in ("half", "sensor") and prime >= 2048:
                     assert chunk.size <= solo.size * 1.03, (ts, kind, chunk.size, solo.size)
     finally:
